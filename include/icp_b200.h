@@ -1,0 +1,141 @@
+/*
+ * icp_b200.h — C-ABI of the B200-native ICP hot path (libicp_b200.so).
+ *
+ * Drop-in boundary for the per-iteration path of yassram/iterative-closest-point:
+ *   closest_matrix -> centroid / cross-covariance -> Horn alignment (s, R, t) -> transform + residual,
+ * iterated by find_corresponding.  Every entry point names the reference interface it replaces
+ * (file:line relative to the reference repository).  Plain pointers and sizes only; no C++/torch
+ * types.  All functions return ICP_OK (0) or a negative icp_status; nothing here ever calls exit().
+ *
+ * Conventions
+ *   - Clouds cross this boundary as `n` points of 3 doubles, x0 y0 z0 x1 y1 z1 ...  This is exactly the
+ *     in-memory image of the reference's column-major 3 x n Eigen::MatrixXd (src/cpu.hh:9-12), so a
+ *     maintainer passes `matrix.data()` and `matrix.cols()` unchanged.
+ *   - 3x3 matrices (R, sr) are row-major double[9]; vectors are double[3].
+ *   - The caller owns every host buffer; the context owns all device memory.  One context per host
+ *     thread; calls are synchronous with respect to their outputs.
+ *   - There is no CPU fallback: every call that computes needs a CUDA device and fails with
+ *     ICP_ERR_CUDA / ICP_ERR_NO_DEVICE otherwise.
+ *   - Correspondence indices are bit-exact with the reference's FP64 argmin
+ *     (sqrt(dx^2+dy^2+dz^2), first minimum wins, src/cpu.cc:14-22): an FP32 brute-force filter is
+ *     followed by an FP64 re-rank that evaluates the reference's expression on every candidate
+ *     the filter could not rule out with a rigorous error bound.
+ */
+#ifndef ICP_B200_H
+#define ICP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum icp_status {
+    ICP_OK = 0,
+    ICP_ERR_INVALID = -1,      /* bad argument / call order (e.g. no model set) */
+    ICP_ERR_NO_DEVICE = -2,    /* no usable CUDA device: there is no CPU fallback */
+    ICP_ERR_CUDA = -3,         /* a CUDA runtime call failed; see icp_last_error() */
+    ICP_ERR_SIZE_MISMATCH = -4,/* np != nm   — reference: exit(-1), src/cpu.cc:44-47 */
+    ICP_ERR_TOO_FEW = -5,      /* np < 4     — reference: exit(-1), src/cpu.cc:49-52 */
+    ICP_ERR_COMM = -6          /* NCCL unavailable or a collective failed */
+} icp_status;
+
+typedef struct icp_ctx icp_ctx;
+
+/* Counters of the last icp_closest / icp_run on this context (device work only). */
+typedef struct icp_stats {
+    int64_t np, nm;             /* points held by this context (scene shard, model) */
+    int64_t nn_calls;           /* closest-matrix passes executed */
+    int64_t nn_pairs;           /* distance evaluations = sum over passes of np*nm */
+    int64_t rerank_full;        /* scene points sent to the full FP64 scan (filter ambiguous) */
+    int64_t rerank_chunk;       /* scene points resolved by the FP64 re-rank of one model chunk */
+    int32_t n_splits;           /* model splits of the 2-D decomposition */
+    int32_t tile_points;        /* scene points per CTA */
+    int32_t chunk_points;       /* model points per tracking chunk */
+    int32_t kernels_launched;   /* kernels launched by the last icp_run / operator call */
+    float   ms_filter;          /* CUDA-event time of the FP32 filter kernel, summed over the last run */
+    float   ms_total;           /* CUDA-event time of the last icp_run (device loop only) */
+} icp_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+
+/* Creates a context on CUDA device `device` (streams, scratch).  Replaces nothing in the reference
+ * (its wrappers allocate and free per call, src/GPU/compute.cu:154-245,348-379). */
+int icp_create(icp_ctx** ctx, int device);
+void icp_destroy(icp_ctx* ctx);
+const char* icp_last_error(void);
+const char* icp_version(void);
+
+/* ---- state: the ICP object (reference: CPU::ICP ctor src/cpu.hh:48-60, GPU::ICP src/GPU/gpu.hh:44-57)
+ * icp_set_model  <- `m` (3 x nm).  Builds the FP64 SoA master and the FP32 shadow; uploaded once
+ *                   (reference re-uploads every call: Matrix::toGpu, src/GPU/compute.cu:29-41).
+ * icp_set_scene  <- `p` / `new_p` (3 x np).  Resets s = 1, R = I, t = 0 like the ctor.
+ * icp_get_scene  -> `new_p` (src/cpu.hh:97).
+ * icp_reset_scene   restores new_p to the cloud given to the last icp_set_scene without a host copy. */
+int icp_set_model(icp_ctx* ctx, const double* m_xyz, int64_t nm);
+int icp_set_scene(icp_ctx* ctx, const double* p_xyz, int64_t np);
+int icp_get_scene(icp_ctx* ctx, double* p_xyz_out);
+int icp_reset_scene(icp_ctx* ctx);
+
+/* ---- operators -------------------------------------------------------------------------------
+ * icp_closest          CPU::closest_matrix(closest_matrix_params)   src/cpu.cc:5-27
+ *                      compute_Y_w_opti(m, p, Y)                     src/GPU/gpu.hh:110, compute.cu:154-245
+ *                      idx_out[j] (nullable) = argmin index, Y_out (nullable) = m[:, idx[j]].
+ * icp_centroid         row means of new_p and Y                      src/cpu.cc:113-114 (bench.cc:146-157)
+ * icp_find_alignment   CPU::ICP::find_alignment(Y)                   src/cpu.cc:105-175, src/GPU/gpu.cc:95-151
+ *                      on the current correspondences; updates the context's s, R, t and returns
+ *                      err_compute_alignment (src/cpu.cc:93-103) in *err_align.
+ * icp_err_compute      in_place = 1: CPU::err_compute                 src/cpu.cc:29-40  (new_p <- sR new_p + t)
+ *                      in_place = 0: CPU::err_compute_alignment       src/cpu.cc:93-103
+ *                      mirrors compute_err_w's flag                   src/GPU/gpu.hh:112-113
+ * icp_get_transform    the context's current s, R, t                  src/cpu.hh:100-103 */
+int icp_closest(icp_ctx* ctx, int32_t* idx_out, double* Y_xyz_out);
+int icp_centroid(icp_ctx* ctx, double mu_p[3], double mu_y[3]);
+int icp_find_alignment(icp_ctx* ctx, double* s, double R[9], double t[3], double* err_align);
+int icp_err_compute(icp_ctx* ctx, int in_place, double* err);
+int icp_get_transform(icp_ctx* ctx, double* s, double R[9], double t[3]);
+
+/* ---- the loop --------------------------------------------------------------------------------
+ * icp_run              CPU::ICP::find_corresponding()                 src/cpu.cc:55-79
+ *                      GPU::ICP::find_corresponding_opti()            src/GPU/gpu.cc:52-83
+ * Runs up to max_iter iterations entirely on the device; stops after the first iteration whose
+ * error value (src/cpu.cc:65-73: (err_alignment + err_compute) / np) is < threshold
+ * (reference: 1e-5, src/cpu.hh:113).  err_hist (nullable, max_iter doubles) receives the value the
+ * reference prints each iteration.  check_sizes != 0 applies alignement_check (src/cpu.cc:42-53)
+ * and returns ICP_ERR_SIZE_MISMATCH / ICP_ERR_TOO_FEW where the reference exits. */
+int icp_run(icp_ctx* ctx, int max_iter, double threshold, int check_sizes, int* iters_done, double* err_hist);
+
+/* Correspondence indices of the last closest pass (any of icp_closest / icp_run). */
+int icp_get_indices(icp_ctx* ctx, int32_t* idx_out);
+int icp_get_stats(icp_ctx* ctx, icp_stats* out);
+
+/* ---- stateless one-shot forms (host pointers in, host results out) — back the reference-shaped
+ * wrappers of src/GPU/gpu.hh:110-116; each creates and destroys a context on device 0.
+ * icp_closest_matrix_host   compute_Y_w_opti / CPU::closest_matrix
+ * icp_nearest_index_host    compute_distance_w_naive(m, pi) -> int     src/GPU/compute.cu:279-308
+ * icp_err_compute_host      compute_err_w(Y, p, in_place, sr, t)        src/GPU/compute.cu:348-379
+ * icp_subtract_col_host     substract_col_w(M, m)                       src/GPU/compute.cu:400-416
+ * icp_y_p_norm_host         y_p_norm_w(y, p, n, d_caps, sp)             src/GPU/compute.cu:442-469 */
+int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np,
+                            int32_t* idx_out, double* Y_xyz_out);
+int icp_nearest_index_host(const double* m_xyz, int64_t nm, const double pi[3], int32_t* idx_out);
+int icp_err_compute_host(const double* Y_xyz, double* p_xyz, int64_t np, int in_place,
+                         const double sr[9], const double t[3], double* err);
+int icp_subtract_col_host(const double* M_xyz, int64_t n, const double m[3], double* out_xyz);
+int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, double* d_caps, double* sp);
+
+/* ---- multi-GPU (new; the reference is single-GPU) ----------------------------------------------
+ * One context per GPU / rank holds a contiguous block of the scene and a replica of the model.
+ * The per-iteration exchange is an all-reduce(sum) of 18 doubles of moments and of 1 double of
+ * residual, issued in-stream through NCCL.  icp_comm_unique_id fills a 128-byte NCCL unique id
+ * (rank 0 creates it, the launcher broadcasts it); icp_comm_init joins the communicator.
+ * nccl_library_path may be NULL ("libnccl.so.2" is resolved by the dynamic loader).
+ * With a communicator attached, `np` in the error value and in the means is the GLOBAL scene size. */
+int icp_comm_unique_id(const char* nccl_library_path, void* id128);
+int icp_comm_init(icp_ctx* ctx, const char* nccl_library_path, const void* id128, int rank, int world);
+int icp_comm_world(icp_ctx* ctx, int* rank, int* world);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ICP_B200_H */

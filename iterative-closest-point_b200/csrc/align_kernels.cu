@@ -1,0 +1,528 @@
+// align_kernels.cu — K2 (fused moments), K3 (Horn quaternion solve), K4 (fused transform + residual)
+// for sm_100a.  All FP64, HBM-bound linear passes; they replace, without porting,
+//   host means + substract_col + host 3xn.nx3 product + y_p_norm   (src/GPU/gpu.cc:98-104,142; compute.cu:381-440)
+//   host Eigen::EigenSolver on Horn's N                             (src/cpu.cc:121-152, src/GPU/gpu.cc:106-140)
+//   compute_err (both uses)                                         (src/GPU/compute.cu:315-379; src/cpu.cc:29-40,93-103)
+//
+// K2 reads each scene point once (24 B) with its correspondence (4 B) and the gathered model point
+// (24 B) and accumulates 18 sums about the pivot c0 (centre of the model's bounding box):
+//   n, sum a, sum b, sum a b^T, sum |a|^2, sum |b|^2      with a = p - c0, b = y - c0.
+// Centring is algebraic (S = sum a b^T - n mu_a mu_b^T, ...), so the centred copies p', y' that the
+// reference materialises (src/cpu.cc:116-117) never exist.  Reduction is a fixed two-level tree
+// (block partials -> last block), so results are run-to-run deterministic.
+#include "icp_common.cuh"
+
+namespace icpb {
+
+namespace {
+
+// block-wide sum of N doubles held per thread; result valid in thread 0
+template <int N>
+__device__ __forceinline__ void block_sum(double (&v)[N], double* smem /* N * warps */)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = warp_sum(v[i]);
+    if (lane == 0)
+#pragma unroll
+        for (int i = 0; i < N; ++i) smem[i * nw + w] = v[i];
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            double x = lane < nw ? smem[i * nw + lane] : 0.0;
+            v[i] = warp_sum(x);
+        }
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: moments.
+__global__ void __launch_bounds__(RED_THREADS)
+moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
+               const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
+               const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
+               double* __restrict__ mom, int* __restrict__ ctl, int honor_done)
+{
+    if (honor_done && ctl[CTL_DONE]) return;
+    __shared__ double red[17 * (RED_THREADS / 32)];
+    __shared__ int is_last;
+    const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
+    double acc[17];
+#pragma unroll
+    for (int i = 0; i < 17; ++i) acc[i] = 0.0;
+    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < np; j += gridDim.x * RED_THREADS) {
+        const int k = idx[j];
+        const double ax = p64x[j] - c0x, ay = p64y[j] - c0y, az = p64z[j] - c0z;
+        const double bx = m64x[k] - c0x, by = m64y[k] - c0y, bz = m64z[k] - c0z;
+        acc[0] += ax; acc[1] += ay; acc[2] += az;
+        acc[3] += bx; acc[4] += by; acc[5] += bz;
+        acc[6] += ax * bx; acc[7] += ax * by; acc[8] += ax * bz;
+        acc[9] += ay * bx; acc[10] += ay * by; acc[11] += ay * bz;
+        acc[12] += az * bx; acc[13] += az * by; acc[14] += az * bz;
+        acc[15] += ax * ax + ay * ay + az * az;
+        acc[16] += bx * bx + by * by + bz * bz;
+    }
+    block_sum<17>(acc, red);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < 17; ++i) partials[(size_t)blockIdx.x * 17 + i] = acc[i];
+        __threadfence();
+        const int t = atomicAdd(&ctl[CTL_TICKET_MOM], 1);
+        is_last = (t == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double tot[17];
+#pragma unroll
+        for (int i = 0; i < 17; ++i) tot[i] = 0.0;
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS)
+#pragma unroll
+            for (int i = 0; i < 17; ++i) tot[i] += partials[(size_t)b * 17 + i];
+        block_sum<17>(tot, red);
+        if (threadIdx.x == 0) {
+            mom[0] = (double)np;
+#pragma unroll
+            for (int i = 0; i < 17; ++i) mom[1 + i] = tot[i];
+            ctl[CTL_TICKET_MOM] = 0;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: Horn's closed form.  One warp; the 4x4 symmetric eigenproblem is solved with cyclic Jacobi by
+// lane 0 (a few hundred FP64 flops) and the eigenvector of the LARGEST eigenvalue is taken — the
+// rule the reference intends (src/cpu.cc:131; its max_element_index has a bug, see oracle).
+__device__ void jacobi4_dev(double A[4][4], double V[4][4])
+{
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) V[i][j] = (i == j) ? 1.0 : 0.0;
+    for (int sweep = 0; sweep < 32; ++sweep) {
+        double off = 0.0;
+        for (int i = 0; i < 4; ++i)
+            for (int j = i + 1; j < 4; ++j) off += A[i][j] * A[i][j];
+        if (off == 0.0) break;
+        for (int p = 0; p < 3; ++p)
+            for (int q = p + 1; q < 4; ++q) {
+                const double apq = A[p][q];
+                if (apq == 0.0) continue;
+                const double theta = (A[q][q] - A[p][p]) / (2.0 * apq);
+                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+                for (int k = 0; k < 4; ++k) {
+                    const double akp = A[k][p], akq = A[k][q];
+                    A[k][p] = c * akp - s * akq;
+                    A[k][q] = s * akp + c * akq;
+                }
+                for (int k = 0; k < 4; ++k) {
+                    const double apk = A[p][k], aqk = A[q][k];
+                    A[p][k] = c * apk - s * aqk;
+                    A[q][k] = s * apk + c * aqk;
+                }
+                for (int k = 0; k < 4; ++k) {
+                    const double vkp = V[k][p], vkq = V[k][q];
+                    V[k][p] = c * vkp - s * vkq;
+                    V[k][q] = s * vkp + c * vkq;
+                }
+            }
+    }
+}
+
+__global__ void solve_kernel(const double* __restrict__ geo, const double* __restrict__ mom, double* __restrict__ xf,
+                             const int* __restrict__ ctl, int honor_done)
+{
+    if (honor_done && ctl[CTL_DONE]) return;
+    if (threadIdx.x != 0) return;
+    const double n = mom[0];
+    const double mua[3] = {mom[1] / n, mom[2] / n, mom[3] / n};
+    const double mub[3] = {mom[4] / n, mom[5] / n, mom[6] / n};
+    double S[3][3];
+    for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < 3; ++b) S[a][b] = mom[7 + a * 3 + b] - n * mua[a] * mub[b];   // src/cpu.cc:119
+    // Horn's N, src/cpu.cc:121-126
+    double N[4][4] = {
+        {S[0][0] + S[1][1] + S[2][2], S[1][2] - S[2][1], S[2][0] - S[0][2], S[0][1] - S[1][0]},
+        {S[1][2] - S[2][1], S[0][0] - S[2][2] - S[1][1], S[0][1] + S[1][0], S[0][2] + S[2][0]},
+        {S[2][0] - S[0][2], S[1][0] + S[0][1], S[1][1] - S[2][2] - S[0][0], S[1][2] + S[2][1]},
+        {S[0][1] - S[1][0], S[2][0] + S[0][2], S[2][1] + S[1][2], S[2][2] - S[1][1] - S[0][0]}};
+    double V[4][4];
+    jacobi4_dev(N, V);
+    int kmax = 0;
+    for (int i = 1; i < 4; ++i)
+        if (N[i][i] > N[kmax][kmax]) kmax = i;
+    const double q0 = V[0][kmax], q1 = V[1][kmax], q2 = V[2][kmax], q3 = V[3][kmax];
+    // R = (q_bar^T q_caps)[1:4,1:4], src/cpu.cc:138-152
+    const double qb[4][4] = {{q0, -q1, -q2, -q3}, {q1, q0, q3, -q2}, {q2, -q3, q0, q1}, {q3, q2, -q1, q0}};
+    const double qc[4][4] = {{q0, -q1, -q2, -q3}, {q1, q0, -q3, q2}, {q2, q3, q0, -q1}, {q3, -q2, q1, q0}};
+    double R[9];
+    for (int i = 1; i < 4; ++i)
+        for (int j = 1; j < 4; ++j) {
+            double acc = 0.0;
+            for (int k = 0; k < 4; ++k) acc += qb[k][i] * qc[k][j];
+            R[(i - 1) * 3 + (j - 1)] = acc;
+        }
+    // scale and translation, src/cpu.cc:154-167
+    const double d_caps = mom[17] - n * (mub[0] * mub[0] + mub[1] * mub[1] + mub[2] * mub[2]);
+    const double sp = mom[16] - n * (mua[0] * mua[0] + mua[1] * mua[1] + mua[2] * mua[2]);
+    const double s = sqrt(d_caps / sp);
+    const double mup[3] = {mua[0] + geo[0], mua[1] + geo[1], mua[2] + geo[2]};
+    const double muy[3] = {mub[0] + geo[0], mub[1] + geo[1], mub[2] + geo[2]};
+    xf[0] = s;
+    for (int i = 0; i < 9; ++i) xf[1 + i] = R[i];
+    for (int a = 0; a < 3; ++a)
+        xf[10 + a] = muy[a] - ((s * R[a * 3] * mup[0] + s * R[a * 3 + 1] * mup[1]) + s * R[a * 3 + 2] * mup[2]);
+    for (int a = 0; a < 3; ++a) { xf[13 + a] = mup[a]; xf[16 + a] = muy[a]; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: fused transform + residual.  Per point q = sR p + t (evaluated as the reference does:
+// sr = s*R element-wise, then (sr0 x + sr1 y + sr2 z) + t, no FMA contraction), e = |y - q|^2.
+// in_place = 1 (CPU::err_compute, src/cpu.cc:29-40): q overwrites new_p (FP64 master + FP32 shadow).
+// in_place = 0 (CPU::err_compute_alignment, src/cpu.cc:93-103): residual only.
+// finish = 1: the last block also closes the ICP iteration (src/cpu.cc:67-77): the reference adds the
+// two residual sums, which are the same expression evaluated twice, so err = 2*sum/np.
+__global__ void __launch_bounds__(RED_THREADS)
+transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
+                 const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
+                 double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
+                 const int32_t* __restrict__ idx, int np, int np_pad, const double* __restrict__ xf, int in_place,
+                 double* __restrict__ partials, double* __restrict__ err_sum, int* __restrict__ ctl, int honor_done,
+                 int finish, double n_global, double threshold, double* __restrict__ err_hist)
+{
+    if (honor_done && ctl[CTL_DONE]) return;
+    __shared__ double red[RED_THREADS / 32];
+    __shared__ int is_last;
+    const double s = xf[0];
+    double sr[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(s, xf[1 + i]);
+    const double tx = xf[10], ty = xf[11], tz = xf[12];
+    const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
+    double acc[1] = {0.0};
+    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < np; j += gridDim.x * RED_THREADS) {
+        const int k = idx[j];
+        const double x = p64x[j], y = p64y[j], z = p64z[j];
+        const double qx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
+        const double qy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
+        const double qz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
+        const double ex = __dsub_rn(m64x[k], qx), ey = __dsub_rn(m64y[k], qy), ez = __dsub_rn(m64z[k], qz);
+        acc[0] += __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
+        if (in_place) {
+            p64x[j] = qx; p64y[j] = qy; p64z[j] = qz;
+            const float fx = (float)(qx - c0x), fy = (float)(qy - c0y), fz = (float)(qz - c0z);
+            phx[j] = fx; phy[j] = fy; phz[j] = fz;
+            if (j == np - 1)   // keep the padding of the FP32 shadow equal to the last real point
+                for (int q = np; q < np_pad; ++q) { phx[q] = fx; phy[q] = fy; phz[q] = fz; }
+        }
+    }
+    block_sum<1>(acc, red);
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = acc[0];
+        __threadfence();
+        const int t = atomicAdd(&ctl[CTL_TICKET_ERR], 1);
+        is_last = (t == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double tot[1] = {0.0};
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS) tot[0] += partials[b];
+        block_sum<1>(tot, red);
+        if (threadIdx.x == 0) {
+            err_sum[0] = tot[0];
+            ctl[CTL_TICKET_ERR] = 0;
+            if (finish) {
+                const int it = ctl[CTL_ITERS];
+                const double err = (tot[0] + tot[0]) / n_global;
+                err_hist[it] = err;
+                ctl[CTL_ITERS] = it + 1;
+                if (err < threshold) ctl[CTL_DONE] = 1;
+            }
+        }
+    }
+}
+
+// Multi-GPU: closes the iteration after the residual sums have been all-reduced.
+__global__ void finish_kernel(const double* __restrict__ err_sum, double n_global, double threshold,
+                              double* __restrict__ err_hist, int* __restrict__ ctl)
+{
+    if (ctl[CTL_DONE]) return;
+    const int it = ctl[CTL_ITERS];
+    const double err = (err_sum[0] + err_sum[0]) / n_global;
+    err_hist[it] = err;
+    ctl[CTL_ITERS] = it + 1;
+    if (err < threshold) ctl[CTL_DONE] = 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Preparation kernels (run once per icp_set_model / icp_set_scene, not per iteration).
+
+// Bounding box of an AoS FP64 cloud: single block, out = min[3], max[3].
+__global__ void __launch_bounds__(1024) bbox_kernel(const double* __restrict__ xyz, int64_t n, double* __restrict__ out)
+{
+    __shared__ double smin[3][32], smax[3][32];
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const double v = xyz[3 * i + c];
+            mn[c] = fmin(mn[c], v);
+            mx[c] = fmax(mx[c], v);
+        }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[c] = fmin(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+            mx[c] = fmax(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+        }
+        if (lane == 0) { smin[c][w] = mn[c]; smax[c][w] = mx[c]; }
+    }
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            double a = lane < (int)(blockDim.x >> 5) ? smin[c][lane] : 1e300;
+            double b = lane < (int)(blockDim.x >> 5) ? smax[c][lane] : -1e300;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a = fmin(a, __shfl_xor_sync(0xffffffffu, a, o));
+                b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+            }
+            if (lane == 0) { out[c] = a; out[3 + c] = b; }
+        }
+    }
+}
+
+// geo[4..9] = bbox  ->  geo[0..2] = c0 (bbox centre), geo[3] = Rm >= max |m - c0|
+__global__ void model_geo_kernel(double* geo)
+{
+    double h2 = 0.0;
+    for (int c = 0; c < 3; ++c) {
+        const double lo = geo[4 + c], hi = geo[7 + c];
+        geo[c] = 0.5 * (lo + hi);
+        const double h = fmax(hi - geo[c], geo[c] - lo);
+        h2 += h * h;
+    }
+    geo[3] = sqrt(h2) * (1.0 + 1e-9);
+}
+
+// AoS FP64 model -> FP64 SoA master + FP32 float4 shadow (c0-relative), sentinel padding.
+__global__ void model_build_kernel(const double* __restrict__ xyz, int64_t nm, int64_t nm_pad,
+                                   const double* __restrict__ geo, double* __restrict__ m64x,
+                                   double* __restrict__ m64y, double* __restrict__ m64z, float4* __restrict__ mhat)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nm_pad) return;
+    if (i < nm) {
+        const double x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+        m64x[i] = x; m64y[i] = y; m64z[i] = z;
+        mhat[i] = make_float4((float)(x - geo[0]), (float)(y - geo[1]), (float)(z - geo[2]), 0.f);
+    } else {
+        mhat[i] = make_float4(NN_SENTINEL, NN_SENTINEL, NN_SENTINEL, 0.f);
+    }
+}
+
+__device__ __forceinline__ uint32_t spread10(uint32_t v)
+{
+    v &= 0x3ffu;
+    v = (v | (v << 16)) & 0x030000ffu;
+    v = (v | (v << 8)) & 0x0300f00fu;
+    v = (v | (v << 4)) & 0x030c30c3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+
+// 30-bit Morton keys over the scene's own bounding box.
+__global__ void scene_keys_kernel(const double* __restrict__ xyz, int64_t n, const double* __restrict__ bbox,
+                                  uint32_t* __restrict__ keys, int32_t* __restrict__ vals)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t q[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const double lo = bbox[c], ext = bbox[3 + c] - lo;
+        double f = ext > 0.0 ? (xyz[3 * i + c] - lo) / ext : 0.0;
+        f = fmin(fmax(f, 0.0), 1.0);
+        q[c] = (uint32_t)fmin(f * 1024.0, 1023.0);
+    }
+    keys[i] = (spread10(q[0]) << 2) | (spread10(q[1]) << 1) | spread10(q[2]);
+    vals[i] = (int32_t)i;
+}
+
+// Gather the scene into sorted SoA order: FP64 master, backup, FP32 shadow (+ padding = last point).
+__global__ void scene_build_kernel(const double* __restrict__ xyz, int64_t np, int64_t np_pad,
+                                   const int32_t* __restrict__ perm, const double* __restrict__ geo,
+                                   double* __restrict__ p64x, double* __restrict__ p64y, double* __restrict__ p64z,
+                                   double* __restrict__ q64x, double* __restrict__ q64y, double* __restrict__ q64z,
+                                   float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np_pad) return;
+    const int64_t src = perm[i < np ? i : np - 1];
+    const double x = xyz[3 * src], y = xyz[3 * src + 1], z = xyz[3 * src + 2];
+    if (i < np) {
+        p64x[i] = x; p64y[i] = y; p64z[i] = z;
+        q64x[i] = x; q64y[i] = y; q64z[i] = z;
+    }
+    phx[i] = (float)(x - geo[0]); phy[i] = (float)(y - geo[1]); phz[i] = (float)(z - geo[2]);
+}
+
+__global__ void scene_restore_kernel(int64_t np, int64_t np_pad, const double* __restrict__ geo,
+                                     const double* __restrict__ q64x, const double* __restrict__ q64y,
+                                     const double* __restrict__ q64z, double* __restrict__ p64x,
+                                     double* __restrict__ p64y, double* __restrict__ p64z, float* __restrict__ phx,
+                                     float* __restrict__ phy, float* __restrict__ phz)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np_pad) return;
+    const int64_t src = i < np ? i : np - 1;
+    const double x = q64x[src], y = q64y[src], z = q64z[src];
+    if (i < np) { p64x[i] = x; p64y[i] = y; p64z[i] = z; }
+    phx[i] = (float)(x - geo[0]); phy[i] = (float)(y - geo[1]); phz[i] = (float)(z - geo[2]);
+}
+
+__global__ void scene_export_kernel(int64_t np, const int32_t* __restrict__ perm, const double* __restrict__ p64x,
+                                    const double* __restrict__ p64y, const double* __restrict__ p64z,
+                                    double* __restrict__ out)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np) return;
+    const int64_t d = perm[i];
+    out[3 * d] = p64x[i]; out[3 * d + 1] = p64y[i]; out[3 * d + 2] = p64z[i];
+}
+
+__global__ void indices_export_kernel(int64_t np, const int32_t* __restrict__ perm, const int32_t* __restrict__ idx,
+                                      const double* __restrict__ m64x, const double* __restrict__ m64y,
+                                      const double* __restrict__ m64z, int32_t* __restrict__ idx_out,
+                                      double* __restrict__ Y_out)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np) return;
+    const int64_t d = perm[i];
+    const int k = idx[i];
+    if (idx_out) idx_out[d] = k;
+    if (Y_out) { Y_out[3 * d] = m64x[k]; Y_out[3 * d + 1] = m64y[k]; Y_out[3 * d + 2] = m64z[k]; }
+}
+
+// mu_p, mu_y from the moments (src/cpu.cc:113-114)
+__global__ void centroid_export_kernel(const double* __restrict__ geo, const double* __restrict__ mom,
+                                       double* __restrict__ out6)
+{
+    const double n = mom[0];
+    for (int c = 0; c < 3; ++c) {
+        out6[c] = mom[1 + c] / n + geo[c];
+        out6[3 + c] = mom[4 + c] / n + geo[c];
+    }
+}
+
+// substract_col (src/GPU/compute.cu:381-398): out[:,i] = M[:,i] - m
+__global__ void subtract_col_kernel(const double* __restrict__ M, int64_t n, double mx, double my, double mz,
+                                    double* __restrict__ out)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[3 * i] = M[3 * i] - mx; out[3 * i + 1] = M[3 * i + 1] - my; out[3 * i + 2] = M[3 * i + 2] - mz;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+static inline int grid1d(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+int reduce_blocks_for(int64_t n, int sm_count)
+{
+    int64_t b = (n + RED_THREADS - 1) / RED_THREADS;
+    const int64_t cap = (int64_t)sm_count * 4;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
+                    int honor_done, cudaStream_t st)
+{
+    moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
+                                                     (int)s.np, partials, mom, ctl, honor_done);
+}
+
+void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st)
+{
+    solve_kernel<<<1, 32, 0, st>>>(m.geo, mom, xf, ctl, honor_done);
+}
+
+void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, int in_place, double* partials,
+                      int n_blocks, double* err_sum, int* ctl, int honor_done, int finish, double n_global,
+                      double threshold, double* err_hist, cudaStream_t st)
+{
+    transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
+                                                       s.phy, s.phz, s.idx, (int)s.np, (int)s.np_pad, xf, in_place,
+                                                       partials, err_sum, ctl, honor_done, finish, n_global,
+                                                       threshold, err_hist);
+}
+
+void launch_finish(const double* err_sum, double n_global, double threshold, double* err_hist, int* ctl,
+                   cudaStream_t st)
+{
+    finish_kernel<<<1, 1, 0, st>>>(err_sum, n_global, threshold, err_hist, ctl);
+}
+
+void launch_bbox(const double* xyz_aos, int64_t n, double* out_min3_max3, cudaStream_t st)
+{
+    bbox_kernel<<<1, 1024, 0, st>>>(xyz_aos, n, out_min3_max3);
+}
+
+void launch_model_geo(double* geo, cudaStream_t st) { model_geo_kernel<<<1, 1, 0, st>>>(geo); }
+
+void launch_model_build(const double* xyz_aos, const ModelDev& m, cudaStream_t st)
+{
+    model_build_kernel<<<grid1d(m.nm_pad, 256), 256, 0, st>>>(xyz_aos, m.nm, m.nm_pad, m.geo, m.m64x, m.m64y, m.m64z,
+                                                              m.mhat);
+}
+
+void launch_scene_keys(const double* xyz_aos, int64_t n, const double* bbox, uint32_t* keys, int32_t* vals,
+                       cudaStream_t st)
+{
+    scene_keys_kernel<<<grid1d(n, 256), 256, 0, st>>>(xyz_aos, n, bbox, keys, vals);
+}
+
+void launch_scene_build(const double* xyz_aos, const ModelDev& m, const SceneDev& s, cudaStream_t st)
+{
+    scene_build_kernel<<<grid1d(s.np_pad, 256), 256, 0, st>>>(xyz_aos, s.np, s.np_pad, s.perm, m.geo, s.p64x, s.p64y,
+                                                              s.p64z, s.q64x, s.q64y, s.q64z, s.phx, s.phy, s.phz);
+}
+
+void launch_scene_restore(const ModelDev& m, const SceneDev& s, cudaStream_t st)
+{
+    scene_restore_kernel<<<grid1d(s.np_pad, 256), 256, 0, st>>>(s.np, s.np_pad, m.geo, s.q64x, s.q64y, s.q64z, s.p64x,
+                                                                s.p64y, s.p64z, s.phx, s.phy, s.phz);
+}
+
+void launch_scene_export(const SceneDev& s, double* xyz_aos_out, cudaStream_t st)
+{
+    scene_export_kernel<<<grid1d(s.np, 256), 256, 0, st>>>(s.np, s.perm, s.p64x, s.p64y, s.p64z, xyz_aos_out);
+}
+
+void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_out, double* Y_aos_out, cudaStream_t st)
+{
+    indices_export_kernel<<<grid1d(s.np, 256), 256, 0, st>>>(s.np, s.perm, s.idx, m.m64x, m.m64y, m.m64z, idx_out,
+                                                             Y_aos_out);
+}
+
+void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st)
+{
+    centroid_export_kernel<<<1, 1, 0, st>>>(m.geo, mom, out6);
+}
+
+void launch_subtract_col(const double* M_aos, int64_t n, double mx, double my, double mz, double* out_aos,
+                         cudaStream_t st)
+{
+    subtract_col_kernel<<<grid1d(n, 256), 256, 0, st>>>(M_aos, n, mx, my, mz, out_aos);
+}
+
+}  // namespace icpb

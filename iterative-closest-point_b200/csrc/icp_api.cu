@@ -1,0 +1,703 @@
+// icp_api.cu — context management and the C-ABI of include/icp_b200.h.
+//
+// Everything the reference keeps in CPU::ICP / GPU::ICP (src/cpu.hh:45-114, src/GPU/gpu.hh:41-104)
+// lives in an icp_ctx as device-resident buffers; the per-iteration loop (src/cpu.cc:55-79) is
+// enqueued on one stream with no host round trip: kernels test a device-side `done` flag.
+// There is no CPU fallback anywhere in this file.
+#include <cub/device/device_radix_sort.cuh>
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/icp_b200.h"
+#include "icp_common.cuh"
+
+using namespace icpb;
+
+namespace {
+
+thread_local std::string g_err;
+
+#define CK(call)                                                                                    \
+    do {                                                                                            \
+        cudaError_t e__ = (call);                                                                   \
+        if (e__ != cudaSuccess) {                                                                   \
+            g_err = std::string(#call) + ": " + cudaGetErrorString(e__);                            \
+            return ICP_ERR_CUDA;                                                                    \
+        }                                                                                           \
+    } while (0)
+
+template <class T>
+int dalloc(T** p, size_t n)
+{
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    CK(cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)));
+    return ICP_OK;
+}
+template <class T>
+void dfree(T*& p)
+{
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+// ---- minimal NCCL surface, resolved at run time from the NCCL the launcher already uses ---------
+typedef struct { char internal[128]; } nccl_uid;
+typedef void* nccl_comm;
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(nccl_uid*) = nullptr;
+    int (*CommInitRank)(nccl_comm*, int, nccl_uid, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm, cudaStream_t) = nullptr;
+    int (*CommDestroy)(nccl_comm) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int NCCL_FLOAT64 = 8, NCCL_SUM = 0;
+
+int load_nccl(NcclApi& api, const char* path)
+{
+    if (api.lib) return ICP_OK;
+    const char* p = (path && *path) ? path : "libnccl.so.2";
+    api.lib = dlopen(p, RTLD_NOW | RTLD_GLOBAL);
+    if (!api.lib) { g_err = std::string("dlopen NCCL failed: ") + dlerror(); return ICP_ERR_COMM; }
+    api.GetUniqueId = (int (*)(nccl_uid*))dlsym(api.lib, "ncclGetUniqueId");
+    api.CommInitRank = (int (*)(nccl_comm*, int, nccl_uid, int))dlsym(api.lib, "ncclCommInitRank");
+    api.AllReduce = (int (*)(const void*, void*, size_t, int, int, nccl_comm, cudaStream_t))dlsym(api.lib, "ncclAllReduce");
+    api.CommDestroy = (int (*)(nccl_comm))dlsym(api.lib, "ncclCommDestroy");
+    api.GetErrorString = (const char* (*)(int))dlsym(api.lib, "ncclGetErrorString");
+    if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy) {
+        g_err = "NCCL symbols missing";
+        return ICP_ERR_COMM;
+    }
+    return ICP_OK;
+}
+
+NcclApi g_nccl;
+
+}  // namespace
+
+struct icp_ctx {
+    int device = 0, sm_count = 148;
+    cudaStream_t st = nullptr;
+    ModelDev m;
+    SceneDev s;
+    NNScratch sc;
+    double* d_stage = nullptr; size_t stage_cap = 0;      // AoS staging (doubles)
+    double *d_partials = nullptr, *d_mom = nullptr, *d_xf = nullptr, *d_err_sum = nullptr, *d_out6 = nullptr;
+    double* d_err_hist = nullptr; int err_hist_cap = 0;
+    int* d_ctl = nullptr;
+    int n_red_blocks = 1;
+    uint32_t *d_keys = nullptr, *d_keys_alt = nullptr; int32_t* d_vals = nullptr; void* d_cub = nullptr;
+    size_t cub_bytes = 0, sort_cap = 0;
+    int32_t* d_idx_out = nullptr; size_t idx_out_cap = 0;
+    bool have_model = false, have_scene = false, have_idx = false;
+    icp_stats stats{};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<cudaEvent_t> ev_filter;
+    nccl_comm comm = nullptr; int rank = 0, world = 1;
+    int forced_splits = 0;
+};
+
+namespace {
+
+int ensure_stage(icp_ctx* c, size_t doubles)
+{
+    if (c->stage_cap >= doubles) return ICP_OK;
+    dfree(c->d_stage);
+    CK(cudaMalloc((void**)&c->d_stage, doubles * sizeof(double)));
+    c->stage_cap = doubles;
+    return ICP_OK;
+}
+
+// 2-D decomposition: choose the number of model splits so that the CTAs balance over the SMs.
+void choose_splits(icp_ctx* c)
+{
+    const int n_tiles = (int)(c->s.np_pad / NN_TILE);
+    const int nm_tiles = (int)(c->m.nm_pad / NN_TM);
+    int best_S = 1, best_tps = nm_tiles;
+    double best_cost = 1e300;
+    const int max_S = nm_tiles < 64 ? nm_tiles : 64;
+    for (int S = 1; S <= max_S; ++S) {
+        const int tps = (nm_tiles + S - 1) / S;
+        const int S_eff = (nm_tiles + tps - 1) / tps;
+        if (S_eff != S) continue;
+        const long items = (long)n_tiles * S_eff;
+        const long per_sm = (items + c->sm_count - 1) / c->sm_count;
+        // one CTA per SM leaves a single warp per scheduler: penalise it mildly
+        const double occ_pen = per_sm >= 3 ? 1.0 : (per_sm == 2 ? 1.05 : 1.25);
+        const double cost = (double)per_sm * (tps + 0.5) * occ_pen;
+        if (cost < best_cost - 1e-9) { best_cost = cost; best_S = S_eff; best_tps = tps; }
+    }
+    if (c->forced_splits > 0) {
+        int S = c->forced_splits < nm_tiles ? c->forced_splits : nm_tiles;
+        best_tps = (nm_tiles + S - 1) / S;
+        best_S = (nm_tiles + best_tps - 1) / best_tps;
+    }
+    c->sc.n_splits = best_S;
+    c->sc.tiles_per_split = best_tps;
+}
+
+int ensure_scratch(icp_ctx* c)
+{
+    choose_splits(c);
+    const size_t need = (size_t)c->sc.n_splits * c->s.np_pad;
+    if (c->sc.cap_points < need) {
+        int r;
+        if ((r = dalloc(&c->sc.best, need))) return r;
+        if ((r = dalloc(&c->sc.runner, need))) return r;
+        if ((r = dalloc(&c->sc.chunk, need))) return r;
+        c->sc.cap_points = need;
+    }
+    return ICP_OK;
+}
+
+int allreduce(icp_ctx* c, double* buf, size_t n)
+{
+    if (!c->comm) return ICP_OK;
+    int r = g_nccl.AllReduce(buf, buf, n, NCCL_FLOAT64, NCCL_SUM, c->comm, c->st);
+    if (r != 0) {
+        g_err = std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error");
+        return ICP_ERR_COMM;
+    }
+    return ICP_OK;
+}
+
+// One closest-matrix pass (K1) on the stream.
+void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1)
+{
+    if (e0) cudaEventRecord(e0, c->st);
+    launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
+    if (e1) cudaEventRecord(e1, c->st);
+    launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
+    launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st);
+    c->stats.kernels_launched += 4;
+}
+
+int reset_ctl(icp_ctx* c)
+{
+    CK(cudaMemsetAsync(c->d_ctl, 0, CTL_N * sizeof(int), c->st));
+    return ICP_OK;
+}
+
+int set_identity_xf(icp_ctx* c)
+{
+    double xf[XF_N] = {0};
+    xf[0] = 1.0; xf[1] = 1.0; xf[5] = 1.0; xf[9] = 1.0;
+    CK(cudaMemcpyAsync(c->d_xf, xf, sizeof(xf), cudaMemcpyHostToDevice, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    return ICP_OK;
+}
+
+int pull_amb_stats(icp_ctx* c)
+{
+    int ctl[CTL_N];
+    CK(cudaMemcpyAsync(ctl, c->d_ctl, sizeof(ctl), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    c->stats.rerank_full += ctl[CTL_AMB_TOTAL];
+    c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
+    return ICP_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+extern "C" {
+
+const char* icp_last_error(void) { return g_err.c_str(); }
+const char* icp_version(void) { return "icp_b200 0.1 (sm_100a)"; }
+
+int icp_create(icp_ctx** out, int device)
+{
+    if (!out) return ICP_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+        g_err = "no usable CUDA device (this library has no CPU fallback)";
+        cudaGetLastError();
+        return ICP_ERR_NO_DEVICE;
+    }
+    CK(cudaSetDevice(device));
+    icp_ctx* c = new icp_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&c->ev0));
+    CK(cudaEventCreate(&c->ev1));
+    int r;
+    if ((r = dalloc(&c->d_mom, MOM_N)) || (r = dalloc(&c->d_xf, XF_N)) || (r = dalloc(&c->d_err_sum, 1)) ||
+        (r = dalloc(&c->d_out6, 8)) || (r = dalloc(&c->d_ctl, CTL_N)) || (r = dalloc(&c->m.geo, 16)) ||
+        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 17))) {
+        delete c;
+        return r;
+    }
+    CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
+    if (const char* e = getenv("ICP_NN_SPLITS")) c->forced_splits = atoi(e);
+    if ((r = set_identity_xf(c))) { delete c; return r; }
+    *out = c;
+    return ICP_OK;
+}
+
+void icp_destroy(icp_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->st);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    dfree(c->m.m64x); dfree(c->m.m64y); dfree(c->m.m64z); dfree(c->m.mhat); dfree(c->m.geo);
+    dfree(c->s.p64x); dfree(c->s.p64y); dfree(c->s.p64z); dfree(c->s.q64x); dfree(c->s.q64y); dfree(c->s.q64z);
+    dfree(c->s.phx); dfree(c->s.phy); dfree(c->s.phz); dfree(c->s.perm); dfree(c->s.idx);
+    dfree(c->sc.best); dfree(c->sc.runner); dfree(c->sc.chunk); dfree(c->sc.amb_list);
+    dfree(c->d_stage); dfree(c->d_partials); dfree(c->d_mom); dfree(c->d_xf); dfree(c->d_err_sum); dfree(c->d_out6);
+    dfree(c->d_err_hist); dfree(c->d_ctl); dfree(c->d_keys); dfree(c->d_keys_alt); dfree(c->d_vals);
+    dfree(c->d_idx_out);
+    if (c->d_cub) cudaFree(c->d_cub);
+    for (auto e : c->ev_filter) cudaEventDestroy(e);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->st) cudaStreamDestroy(c->st);
+    delete c;
+}
+
+int icp_set_model(icp_ctx* c, const double* m_xyz, int64_t nm)
+{
+    if (!c || !m_xyz || nm < 1 || nm > 0x7fffff00LL) { g_err = "icp_set_model: bad arguments"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    int r;
+    if ((r = ensure_stage(c, (size_t)nm * 3))) return r;
+    CK(cudaMemcpyAsync(c->d_stage, m_xyz, (size_t)nm * 3 * sizeof(double), cudaMemcpyHostToDevice, c->st));
+    c->m.nm = nm;
+    c->m.nm_pad = (nm + NN_TM - 1) / NN_TM * NN_TM;
+    if ((r = dalloc(&c->m.m64x, (size_t)nm)) || (r = dalloc(&c->m.m64y, (size_t)nm)) ||
+        (r = dalloc(&c->m.m64z, (size_t)nm)) || (r = dalloc(&c->m.mhat, (size_t)c->m.nm_pad)))
+        return r;
+    launch_bbox(c->d_stage, nm, c->m.geo + 4, c->st);
+    launch_model_geo(c->m.geo, c->st);
+    launch_model_build(c->d_stage, c->m, c->st);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->st));
+    c->have_model = true;
+    c->have_idx = false;
+    c->stats.nm = nm;
+    if (c->have_scene) return icp_reset_scene(c);   // FP32 shadow depends on the model's c0
+    return ICP_OK;
+}
+
+int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
+{
+    if (!c || !p_xyz || np < 1 || np > 0x7fffff00LL) { g_err = "icp_set_scene: bad arguments"; return ICP_ERR_INVALID; }
+    if (!c->have_model) { g_err = "icp_set_scene: set the model first"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    int r;
+    if ((r = ensure_stage(c, (size_t)np * 3 + 8))) return r;
+    CK(cudaMemcpyAsync(c->d_stage, p_xyz, (size_t)np * 3 * sizeof(double), cudaMemcpyHostToDevice, c->st));
+    const int64_t np_pad = (np + NN_TILE - 1) / NN_TILE * NN_TILE;
+    if (c->s.np != np || !c->s.p64x) {
+        c->s.np = np; c->s.np_pad = np_pad;
+        if ((r = dalloc(&c->s.p64x, (size_t)np)) || (r = dalloc(&c->s.p64y, (size_t)np)) ||
+            (r = dalloc(&c->s.p64z, (size_t)np)) || (r = dalloc(&c->s.q64x, (size_t)np)) ||
+            (r = dalloc(&c->s.q64y, (size_t)np)) || (r = dalloc(&c->s.q64z, (size_t)np)) ||
+            (r = dalloc(&c->s.phx, (size_t)np_pad)) || (r = dalloc(&c->s.phy, (size_t)np_pad)) ||
+            (r = dalloc(&c->s.phz, (size_t)np_pad)) || (r = dalloc(&c->s.perm, (size_t)np)) ||
+            (r = dalloc(&c->s.idx, (size_t)np)) || (r = dalloc(&c->sc.amb_list, (size_t)np)))
+            return r;
+    }
+    // Morton sort of the scene (once per scene; a similarity transform keeps tiles compact)
+    if (c->sort_cap < (size_t)np) {
+        if ((r = dalloc(&c->d_keys, (size_t)np)) || (r = dalloc(&c->d_keys_alt, (size_t)np)) ||
+            (r = dalloc(&c->d_vals, (size_t)np)))
+            return r;
+        size_t bytes = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->d_keys, c->d_keys_alt, c->d_vals, c->s.perm, (int)np, 0, 30,
+                                        c->st);
+        if (c->d_cub) cudaFree(c->d_cub);
+        CK(cudaMalloc(&c->d_cub, bytes ? bytes : 1));
+        c->cub_bytes = bytes;
+        c->sort_cap = (size_t)np;
+    }
+    double* bbox = c->d_stage + (size_t)np * 3;
+    launch_bbox(c->d_stage, np, bbox, c->st);
+    launch_scene_keys(c->d_stage, np, bbox, c->d_keys, c->d_vals, c->st);
+    size_t bytes = c->cub_bytes;
+    CK(cub::DeviceRadixSort::SortPairs(c->d_cub, bytes, c->d_keys, c->d_keys_alt, c->d_vals, c->s.perm, (int)np, 0, 30,
+                                       c->st));
+    launch_scene_build(c->d_stage, c->m, c->s, c->st);
+    CK(cudaGetLastError());
+    c->n_red_blocks = reduce_blocks_for(np, c->sm_count);
+    if ((r = ensure_scratch(c))) return r;
+    if ((r = set_identity_xf(c))) return r;
+    c->have_scene = true;
+    c->have_idx = false;
+    c->stats.np = np;
+    return ICP_OK;
+}
+
+int icp_reset_scene(icp_ctx* c)
+{
+    if (!c || !c->have_scene) { g_err = "icp_reset_scene: no scene"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    launch_scene_restore(c->m, c->s, c->st);
+    CK(cudaGetLastError());
+    int r;
+    if ((r = ensure_scratch(c))) return r;
+    c->have_idx = false;
+    return set_identity_xf(c);
+}
+
+int icp_get_scene(icp_ctx* c, double* out)
+{
+    if (!c || !out || !c->have_scene) { g_err = "icp_get_scene: no scene"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    int r;
+    if ((r = ensure_stage(c, (size_t)c->s.np * 3))) return r;
+    launch_scene_export(c->s, c->d_stage, c->st);
+    CK(cudaMemcpyAsync(out, c->d_stage, (size_t)c->s.np * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    return ICP_OK;
+}
+
+int icp_get_indices(icp_ctx* c, int32_t* idx_out)
+{
+    if (!c || !idx_out || !c->have_idx) { g_err = "icp_get_indices: no correspondences yet"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    int r;
+    if (c->idx_out_cap < (size_t)c->s.np) {
+        if ((r = dalloc(&c->d_idx_out, (size_t)c->s.np))) return r;
+        c->idx_out_cap = (size_t)c->s.np;
+    }
+    launch_indices_export(c->s, c->m, c->d_idx_out, nullptr, c->st);
+    CK(cudaMemcpyAsync(idx_out, c->d_idx_out, (size_t)c->s.np * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    return ICP_OK;
+}
+
+int icp_closest(icp_ctx* c, int32_t* idx_out, double* Y_out)
+{
+    if (!c || !c->have_model || !c->have_scene) { g_err = "icp_closest: model and scene required"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    int r;
+    if ((r = reset_ctl(c))) return r;
+    c->stats.kernels_launched = 0;
+    CK(cudaEventRecord(c->ev0, c->st));
+    nn_pass(c, 0, nullptr, nullptr);
+    CK(cudaEventRecord(c->ev1, c->st));
+    CK(cudaGetLastError());
+    c->have_idx = true;
+    c->stats.nn_calls += 1;
+    c->stats.nn_pairs += c->s.np * c->m.nm;
+    if (Y_out) {
+        if ((r = ensure_stage(c, (size_t)c->s.np * 3))) return r;
+    }
+    if (idx_out && c->idx_out_cap < (size_t)c->s.np) {
+        if ((r = dalloc(&c->d_idx_out, (size_t)c->s.np))) return r;
+        c->idx_out_cap = (size_t)c->s.np;
+    }
+    if (idx_out || Y_out) {
+        launch_indices_export(c->s, c->m, idx_out ? c->d_idx_out : nullptr, Y_out ? c->d_stage : nullptr, c->st);
+        if (idx_out)
+            CK(cudaMemcpyAsync(idx_out, c->d_idx_out, (size_t)c->s.np * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+        if (Y_out)
+            CK(cudaMemcpyAsync(Y_out, c->d_stage, (size_t)c->s.np * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    }
+    if ((r = pull_amb_stats(c))) return r;
+    cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
+    c->stats.ms_filter = c->stats.ms_total;
+    return ICP_OK;
+}
+
+static int need_idx(icp_ctx* c, const char* who)
+{
+    if (!c || !c->have_model || !c->have_scene || !c->have_idx) {
+        g_err = std::string(who) + ": needs a model, a scene and correspondences (icp_closest first)";
+        return ICP_ERR_INVALID;
+    }
+    return ICP_OK;
+}
+
+int icp_centroid(icp_ctx* c, double mu_p[3], double mu_y[3])
+{
+    int r;
+    if ((r = need_idx(c, "icp_centroid"))) return r;
+    CK(cudaSetDevice(c->device));
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->st);
+    if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+    launch_centroid_export(c->m, c->d_mom, c->d_out6, c->st);
+    double h[6];
+    CK(cudaMemcpyAsync(h, c->d_out6, sizeof(h), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    if (mu_p) memcpy(mu_p, h, 24);
+    if (mu_y) memcpy(mu_y, h + 3, 24);
+    return ICP_OK;
+}
+
+int icp_get_transform(icp_ctx* c, double* s, double R[9], double t[3])
+{
+    if (!c) return ICP_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    double xf[XF_N];
+    CK(cudaMemcpyAsync(xf, c->d_xf, sizeof(xf), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    if (s) *s = xf[0];
+    if (R) memcpy(R, xf + 1, 72);
+    if (t) memcpy(t, xf + 10, 24);
+    return ICP_OK;
+}
+
+int icp_find_alignment(icp_ctx* c, double* s, double R[9], double t[3], double* err_align)
+{
+    int r;
+    if ((r = need_idx(c, "icp_find_alignment"))) return r;
+    CK(cudaSetDevice(c->device));
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->st);
+    if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+    launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 0, c->st);
+    launch_transform(c->m, c->s, c->d_xf, 0, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 0, 0, 1.0, 0.0,
+                     nullptr, c->st);
+    if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+    CK(cudaGetLastError());
+    double e;
+    CK(cudaMemcpyAsync(&e, c->d_err_sum, sizeof(e), cudaMemcpyDeviceToHost, c->st));
+    if ((r = icp_get_transform(c, s, R, t))) return r;
+    if (err_align) *err_align = e;
+    c->stats.kernels_launched = 3;
+    return ICP_OK;
+}
+
+int icp_err_compute(icp_ctx* c, int in_place, double* err)
+{
+    int r;
+    if ((r = need_idx(c, "icp_err_compute"))) return r;
+    CK(cudaSetDevice(c->device));
+    launch_transform(c->m, c->s, c->d_xf, in_place ? 1 : 0, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 0,
+                     0, 1.0, 0.0, nullptr, c->st);
+    if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+    CK(cudaGetLastError());
+    double e;
+    CK(cudaMemcpyAsync(&e, c->d_err_sum, sizeof(e), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    if (err) *err = e;
+    c->stats.kernels_launched = 1;
+    return ICP_OK;
+}
+
+int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* iters_done, double* err_hist)
+{
+    if (!c || !c->have_model || !c->have_scene) { g_err = "icp_run: model and scene required"; return ICP_ERR_INVALID; }
+    CK(cudaSetDevice(c->device));
+    int r;
+    // alignement_check, src/cpu.cc:42-53 (with a communicator the GLOBAL scene size is what counts)
+    double np_glob = (double)c->s.np;
+    if (c->comm) {
+        CK(cudaMemcpyAsync(c->d_err_sum, &np_glob, sizeof(double), cudaMemcpyHostToDevice, c->st));
+        if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+        CK(cudaMemcpyAsync(&np_glob, c->d_err_sum, sizeof(double), cudaMemcpyDeviceToHost, c->st));
+        CK(cudaStreamSynchronize(c->st));
+    }
+    if (check_sizes) {
+        if ((int64_t)np_glob != c->m.nm) { g_err = "Point sets need to have the same number of points."; return ICP_ERR_SIZE_MISMATCH; }
+        if (np_glob < 4) { g_err = "Need at least 4 point pairs"; return ICP_ERR_TOO_FEW; }
+    }
+    if (iters_done) *iters_done = 0;
+    if (max_iter <= 0) return ICP_OK;
+    if (c->err_hist_cap < max_iter) {
+        if ((r = dalloc(&c->d_err_hist, (size_t)max_iter))) return r;
+        c->err_hist_cap = max_iter;
+    }
+    while ((int)c->ev_filter.size() < 2 * max_iter) {
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e));
+        c->ev_filter.push_back(e);
+    }
+    if ((r = reset_ctl(c))) return r;
+    c->stats.kernels_launched = 0;
+    CK(cudaEventRecord(c->ev0, c->st));
+    for (int it = 0; it < max_iter; ++it) {
+        nn_pass(c, 1, c->ev_filter[2 * it], c->ev_filter[2 * it + 1]);
+        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, c->st);
+        if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+        launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
+        launch_transform(c->m, c->s, c->d_xf, 1, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 1,
+                         c->comm ? 0 : 1, np_glob, threshold, c->d_err_hist, c->st);
+        c->stats.kernels_launched += 3;
+        if (c->comm) {
+            if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+            launch_finish(c->d_err_sum, np_glob, threshold, c->d_err_hist, c->d_ctl, c->st);
+            c->stats.kernels_launched += 1;
+        }
+    }
+    CK(cudaEventRecord(c->ev1, c->st));
+    CK(cudaGetLastError());
+    int ctl[CTL_N];
+    CK(cudaMemcpyAsync(ctl, c->d_ctl, sizeof(ctl), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    const int iters = ctl[CTL_ITERS];
+    if (iters_done) *iters_done = iters;
+    if (err_hist && iters > 0)
+        CK(cudaMemcpy(err_hist, c->d_err_hist, (size_t)iters * sizeof(double), cudaMemcpyDeviceToHost));
+    c->have_idx = iters > 0;
+    c->stats.nn_calls += iters;
+    c->stats.nn_pairs += (int64_t)iters * c->s.np * c->m.nm;
+    c->stats.rerank_full += ctl[CTL_AMB_TOTAL];
+    c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
+    cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
+    float f = 0.f;
+    for (int it = 0; it < iters; ++it) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->ev_filter[2 * it], c->ev_filter[2 * it + 1]);
+        f += ms;
+    }
+    c->stats.ms_filter = f;
+    return ICP_OK;
+}
+
+int icp_get_stats(icp_ctx* c, icp_stats* out)
+{
+    if (!c || !out) return ICP_ERR_INVALID;
+    c->stats.n_splits = c->sc.n_splits;
+    c->stats.tile_points = NN_TILE;
+    c->stats.chunk_points = NN_G;
+    *out = c->stats;
+    return ICP_OK;
+}
+
+// ---- stateless one-shot forms (src/GPU/gpu.hh:110-116) -------------------------------------------
+
+int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np, int32_t* idx_out,
+                            double* Y_out)
+{
+    icp_ctx* c = nullptr;
+    int r = icp_create(&c, 0);
+    if (r) return r;
+    if (!(r = icp_set_model(c, m_xyz, nm)) && !(r = icp_set_scene(c, p_xyz, np))) r = icp_closest(c, idx_out, Y_out);
+    icp_destroy(c);
+    return r;
+}
+
+int icp_nearest_index_host(const double* m_xyz, int64_t nm, const double pi[3], int32_t* idx_out)
+{
+    return icp_closest_matrix_host(m_xyz, nm, pi, 1, idx_out, nullptr);
+}
+
+// Pairs p_j with Y_j directly: the "model" is Y and the correspondence is the identity.
+static int pair_ctx(icp_ctx** out, const double* Y_xyz, const double* p_xyz, int64_t n)
+{
+    icp_ctx* c = nullptr;
+    int r = icp_create(&c, 0);
+    if (r) return r;
+    if ((r = icp_set_model(c, Y_xyz, n)) || (r = icp_set_scene(c, p_xyz, n))) { icp_destroy(c); return r; }
+    // sorted position i holds original point perm[i], whose partner is Y[perm[i]]
+    if (cudaMemcpyAsync(c->s.idx, c->s.perm, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToDevice, c->st) != cudaSuccess) {
+        g_err = "pair_ctx: copy failed";
+        icp_destroy(c);
+        return ICP_ERR_CUDA;
+    }
+    c->have_idx = true;
+    *out = c;
+    return ICP_OK;
+}
+
+int icp_err_compute_host(const double* Y_xyz, double* p_xyz, int64_t np, int in_place, const double sr[9],
+                         const double t[3], double* err)
+{
+    if (!Y_xyz || !p_xyz || !sr || !t || np < 1) { g_err = "icp_err_compute_host: bad arguments"; return ICP_ERR_INVALID; }
+    icp_ctx* c = nullptr;
+    int r = pair_ctx(&c, Y_xyz, p_xyz, np);
+    if (r) return r;
+    double xf[XF_N] = {0};
+    xf[0] = 1.0;
+    memcpy(xf + 1, sr, 72);
+    memcpy(xf + 10, t, 24);
+    if (cudaMemcpyAsync(c->d_xf, xf, sizeof(xf), cudaMemcpyHostToDevice, c->st) != cudaSuccess ||
+        cudaStreamSynchronize(c->st) != cudaSuccess) {
+        g_err = "icp_err_compute_host: upload failed";
+        icp_destroy(c);
+        return ICP_ERR_CUDA;
+    }
+    r = icp_err_compute(c, in_place, err);
+    if (!r && in_place) r = icp_get_scene(c, p_xyz);
+    icp_destroy(c);
+    return r;
+}
+
+int icp_subtract_col_host(const double* M_xyz, int64_t n, const double m[3], double* out_xyz)
+{
+    if (!M_xyz || !m || !out_xyz || n < 1) { g_err = "icp_subtract_col_host: bad arguments"; return ICP_ERR_INVALID; }
+    icp_ctx* c = nullptr;
+    int r = icp_create(&c, 0);
+    if (r) return r;
+    if ((r = ensure_stage(c, (size_t)n * 6))) { icp_destroy(c); return r; }
+    cudaError_t e = cudaMemcpyAsync(c->d_stage, M_xyz, (size_t)n * 24, cudaMemcpyHostToDevice, c->st);
+    launch_subtract_col(c->d_stage, n, m[0], m[1], m[2], c->d_stage + (size_t)n * 3, c->st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_xyz, c->d_stage + (size_t)n * 3, (size_t)n * 24, cudaMemcpyDeviceToHost, c->st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+    if (e != cudaSuccess) { g_err = std::string("icp_subtract_col_host: ") + cudaGetErrorString(e); r = ICP_ERR_CUDA; }
+    icp_destroy(c);
+    return r;
+}
+
+int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, double* d_caps, double* sp)
+{
+    if (!y_xyz || !p_xyz || n < 1) { g_err = "icp_y_p_norm_host: bad arguments"; return ICP_ERR_INVALID; }
+    icp_ctx* c = nullptr;
+    int r = pair_ctx(&c, y_xyz, p_xyz, n);
+    if (r) return r;
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->st);
+    double mom[MOM_N], geo[4];
+    cudaError_t e = cudaMemcpyAsync(mom, c->d_mom, sizeof(mom), cudaMemcpyDeviceToHost, c->st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(geo, c->m.geo, sizeof(geo), cudaMemcpyDeviceToHost, c->st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+    if (e != cudaSuccess) { g_err = std::string("icp_y_p_norm_host: ") + cudaGetErrorString(e); icp_destroy(c); return ICP_ERR_CUDA; }
+    // sums were taken about c0: |v|^2 = |a|^2 + 2 c0.a + |c0|^2
+    const double c2 = geo[0] * geo[0] + geo[1] * geo[1] + geo[2] * geo[2];
+    if (sp) *sp = mom[16] + 2.0 * (geo[0] * mom[1] + geo[1] * mom[2] + geo[2] * mom[3]) + (double)n * c2;
+    if (d_caps) *d_caps = mom[17] + 2.0 * (geo[0] * mom[4] + geo[1] * mom[5] + geo[2] * mom[6]) + (double)n * c2;
+    icp_destroy(c);
+    return ICP_OK;
+}
+
+// ---- multi-GPU ----------------------------------------------------------------------------------
+
+int icp_comm_unique_id(const char* nccl_library_path, void* id128)
+{
+    if (!id128) return ICP_ERR_INVALID;
+    int r = load_nccl(g_nccl, nccl_library_path);
+    if (r) return r;
+    nccl_uid id;
+    if (g_nccl.GetUniqueId(&id) != 0) { g_err = "ncclGetUniqueId failed"; return ICP_ERR_COMM; }
+    memcpy(id128, &id, 128);
+    return ICP_OK;
+}
+
+int icp_comm_init(icp_ctx* c, const char* nccl_library_path, const void* id128, int rank, int world)
+{
+    if (!c || !id128 || world < 1 || rank < 0 || rank >= world) { g_err = "icp_comm_init: bad arguments"; return ICP_ERR_INVALID; }
+    int r = load_nccl(g_nccl, nccl_library_path);
+    if (r) return r;
+    CK(cudaSetDevice(c->device));
+    nccl_uid id;
+    memcpy(&id, id128, 128);
+    int e = g_nccl.CommInitRank(&c->comm, world, id, rank);
+    if (e != 0) {
+        g_err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(e) : "error");
+        c->comm = nullptr;
+        return ICP_ERR_COMM;
+    }
+    c->rank = rank;
+    c->world = world;
+    return ICP_OK;
+}
+
+int icp_comm_world(icp_ctx* c, int* rank, int* world)
+{
+    if (!c) return ICP_ERR_INVALID;
+    if (rank) *rank = c->rank;
+    if (world) *world = c->world;
+    return ICP_OK;
+}
+
+}  // extern "C"

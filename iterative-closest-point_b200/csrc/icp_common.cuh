@@ -1,0 +1,109 @@
+// icp_common.cuh — shared declarations of the B200-native ICP hot path (sm_100a only).
+//
+// Device data layout (everything resident in HBM for the life of a context):
+//   model   m64x/y/z  : FP64 SoA master, original order (indices returned are positions here)
+//           mhat      : float4 (x,y,z,0) = fl32(m - c0), c0 = centre of the model's bounding box;
+//                       padded to a multiple of NN_TM with far-away sentinels
+//   scene   p64x/y/z  : FP64 SoA master of new_p, Morton-sorted (perm[i] = original position)
+//           phx/y/z   : FP32 shadow fl32(new_p - c0), padded to a multiple of NN_TILE
+//           idx       : int32 correspondence per sorted scene point
+//   scratch part_*    : per (model split, scene point) filter results; block partials of reductions
+//   state   xf[]      : s, R[9], t[3], mu_p[3], mu_y[3]; ctl[] : done flag, iteration counter, ...
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace icpb {
+
+// ---- nearest-neighbour filter geometry ---------------------------------------------------------
+constexpr int NN_THREADS = 128;                 // threads per CTA
+constexpr int NN_R       = 8;                   // scene points register-blocked per thread
+constexpr int NN_TILE    = NN_THREADS * NN_R;   // scene points per CTA (1024)
+constexpr int NN_G       = 64;                  // model points per tracking chunk
+constexpr int NN_TM      = 512;                 // model points per shared-memory stage
+constexpr float NN_SENTINEL = 1.0e18f;          // coordinate of padded model points (never wins)
+
+// ---- reductions --------------------------------------------------------------------------------
+constexpr int RED_THREADS = 256;
+constexpr int MOM_N = 18;   // n, sum a(3), sum b(3), sum a b^T(9), sum |a|^2, sum |b|^2   (a = p-c0, b = y-c0)
+constexpr int XF_N  = 20;   // s, R[9], t[3], mu_p[3], mu_y[3], spare
+
+// ctl[] slots (int32, device)
+enum { CTL_DONE = 0, CTL_ITERS = 1, CTL_AMB_COUNT = 2, CTL_TICKET_MOM = 3, CTL_TICKET_ERR = 4,
+       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_N = 8 };
+
+struct ModelDev {
+    int64_t nm = 0, nm_pad = 0;
+    double *m64x = nullptr, *m64y = nullptr, *m64z = nullptr;
+    float4* mhat = nullptr;
+    double* geo = nullptr;       // device: c0[3], Rm (upper bound of |m - c0|), bbox min[3], max[3]
+};
+
+struct SceneDev {
+    int64_t np = 0, np_pad = 0;
+    double *p64x = nullptr, *p64y = nullptr, *p64z = nullptr;   // new_p, sorted order
+    double *q64x = nullptr, *q64y = nullptr, *q64z = nullptr;   // backup of the initial scene, sorted order
+    float *phx = nullptr, *phy = nullptr, *phz = nullptr;
+    int32_t* perm = nullptr;     // sorted position -> original position
+    int32_t* idx = nullptr;      // correspondence (sorted order)
+};
+
+struct NNScratch {
+    int n_splits = 0;
+    int tiles_per_split = 0;     // in units of NN_TM model points
+    float* best = nullptr;       // [n_splits][np_pad]
+    float* runner = nullptr;
+    uint32_t* chunk = nullptr;
+    int32_t* amb_list = nullptr; // [np]
+    size_t cap_points = 0;       // allocated n_splits * np_pad
+};
+
+// ---- launchers (defined in nn_kernels.cu / align_kernels.cu) ------------------------------------
+// All launch on `st`, none synchronises.  `ctl` is the device control block; kernels return at entry
+// when ctl[CTL_DONE] != 0 and `honor_done` is set (used by the device-side loop).
+void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc, const int* ctl, int honor_done,
+                      cudaStream_t st);
+void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
+                      cudaStream_t st);
+void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
+                     int sm_count, cudaStream_t st);
+
+void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
+                    int honor_done, cudaStream_t st);
+void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st);
+// in_place: p <- sR p + t (FP64 master and FP32 shadow).  finish: the last block also closes the iteration
+// (err_hist[it] = 2*sum/n, done flag, iteration counter) — single-GPU loop only.
+void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, int in_place, double* partials,
+                      int n_blocks, double* err_sum, int* ctl, int honor_done, int finish, double n_global,
+                      double threshold, double* err_hist, cudaStream_t st);
+void launch_finish(const double* err_sum, double n_global, double threshold, double* err_hist, int* ctl,
+                   cudaStream_t st);
+
+// preparation
+void launch_bbox(const double* xyz_aos, int64_t n, double* out_min3_max3, cudaStream_t st);
+void launch_model_geo(double* geo, cudaStream_t st);   // geo[4..9] bbox -> geo[0..3] = c0, Rm
+void launch_model_build(const double* xyz_aos, const ModelDev& m, cudaStream_t st);
+void launch_scene_keys(const double* xyz_aos, int64_t n, const double* bbox, uint32_t* keys, int32_t* vals,
+                       cudaStream_t st);
+void launch_scene_build(const double* xyz_aos, const ModelDev& m, const SceneDev& s, cudaStream_t st);
+void launch_scene_restore(const ModelDev& m, const SceneDev& s, cudaStream_t st);
+void launch_scene_export(const SceneDev& s, double* xyz_aos_out, cudaStream_t st);   // unsort + interleave
+void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_out, double* Y_aos_out,
+                           cudaStream_t st);
+void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st);
+void launch_subtract_col(const double* M_aos, int64_t n, double mx, double my, double mz, double* out_aos,
+                         cudaStream_t st);
+
+int reduce_blocks_for(int64_t n, int sm_count);
+
+// ---- small device helpers -----------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+#endif
+
+}  // namespace icpb

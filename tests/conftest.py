@@ -1,0 +1,66 @@
+import lzma
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG_DIR = os.path.join(ROOT, "iterative-closest-point_b200")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+for p in (ROOT, PKG_DIR):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def cloud_text_path(name, tmpdir):
+    """Decompress tests/golden/clouds/<name>.txt.xz into tmpdir and return the .txt path."""
+    dst = os.path.join(str(tmpdir), name + ".txt")
+    if not os.path.exists(dst):
+        with lzma.open(os.path.join(GOLDEN, "clouds", name + ".txt.xz"), "rb") as f:
+            data = f.read()
+        with open(dst, "wb") as g:
+            g.write(data)
+    return dst
+
+
+@pytest.fixture(scope="session")
+def cloud_dir(tmp_path_factory):
+    return tmp_path_factory.mktemp("clouds")
+
+
+@pytest.fixture(scope="session")
+def clouds(cloud_dir):
+    """name -> (n, 3) float64, parsed by the oracle's restatement of src/load.cc."""
+    from oracle import oracle as O
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            cache[name] = O.load_matrix(cloud_text_path(name, cloud_dir))
+        return cache[name]
+    return get
+
+
+@pytest.fixture(scope="session")
+def golden():
+    def get(case):
+        return np.load(os.path.join(GOLDEN, case + ".npz"))
+    return get
+
+
+def synthetic_pair(n, seed=0, angle_deg=5.0, noise=1e-3, shuffle=True, shift=(0.05, -0.03, 0.02)):
+    """Model ~ U[-1,1]^3; scene = R m + t + noise, optionally permuted."""
+    rng = np.random.default_rng(seed)
+    m = rng.uniform(-1.0, 1.0, (n, 3))
+    ax = np.array([1.0, 2.0, 3.0]) / np.sqrt(14.0)
+    a = np.deg2rad(angle_deg)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
+    p = m @ R.T + np.asarray(shift, float) + noise * rng.standard_normal((n, 3))
+    perm = rng.permutation(n) if shuffle else np.arange(n)
+    return m, np.ascontiguousarray(p[perm]), perm

@@ -1,0 +1,217 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C-ABI, against the CPU
+oracle on the same inputs and against the committed golden vectors.
+
+Bars (BASELINE.json north_star): correspondence indices bit-exact; s, R, t and the error value within
+1e-5 relative; identical iteration count.
+"""
+import json
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, synthetic_pair
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5   # north_star tolerance for floating-point results
+
+
+@pytest.fixture(scope="module")
+def icp():
+    import icp_b200
+    icp_b200.load_library()
+    return icp_b200
+
+
+def rel(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+# ---- K1: closest_matrix -------------------------------------------------------------------------
+
+@pytest.mark.parametrize("mname,pname", [("cow_ref", "cow_tr1"), ("cow_ref", "cow_tr2"), ("horse_ref", "horse_tr1"),
+                                         ("horse_ref", "horse_tr2"), ("bun000", "bun045"), ("bun045", "bun000")])
+def test_closest_matrix_indices_bit_exact(icp, clouds, mname, pname):
+    m, p = clouds(mname), clouds(pname)
+    idx_o, Y_o = O.closest_matrix(p, m, O.NN_MULSQRT)
+    Y, idx = icp.closest_matrix(p, m, return_index=True)
+    assert np.array_equal(idx, idx_o)
+    assert np.array_equal(Y, Y_o)          # Y columns are copies of model columns: exact
+
+
+def test_closest_small_and_ties(icp):
+    m = np.array([[1.0, 0, 0], [-1.0, 0, 0], [1.0, 0, 0], [0, 5.0, 0]])
+    p = np.array([[0.0, 0, 0], [0.9, 0, 0], [0, 4.0, 0]])
+    Y, idx = icp.closest_matrix(p, m, return_index=True)
+    assert idx.tolist() == [0, 0, 3]       # first minimum wins (Eigen minCoeff, src/cpu.cc:21-22)
+    assert icp.compute_distance_w_naive(m, [0.0, 0.1, 0]) == 0
+    # single model point / single scene point
+    assert icp.closest_matrix(p, m[:1], return_index=True)[1].tolist() == [0, 0, 0]
+
+
+def test_closest_duplicates_across_chunks(icp):
+    # exact duplicates thousands of indices apart: the FP32 filter cannot separate them, the FP64
+    # re-rank must return the lowest index
+    rng = np.random.default_rng(5)
+    base = rng.uniform(-1, 1, (3000, 3))
+    m = np.concatenate([base, base[::-1], base])          # every point three times
+    p = base[rng.permutation(3000)[:777]] + 1e-9
+    idx_o, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
+    _, idx = icp.closest_matrix(p, m, return_index=True)
+    assert np.array_equal(idx, idx_o)
+    assert (idx < 3000).all()
+
+
+def test_closest_near_ties_below_fp32_resolution(icp):
+    # candidates whose distances differ by ~1e-12 relative, on a cloud with a large common offset
+    rng = np.random.default_rng(7)
+    p = rng.uniform(-1, 1, (2048, 3)) + 100.0
+    d = rng.standard_normal((2048, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    r = 0.01
+    m = np.concatenate([p + r * d * (1 + 1e-12), p - r * d, p + r * d[:, [1, 2, 0]] * (1 + 3e-12)])
+    m = m[rng.permutation(len(m))]
+    idx_o, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
+    _, idx = icp.closest_matrix(p, m, return_index=True)
+    assert np.array_equal(idx, idx_o)
+
+
+@pytest.mark.parametrize("n,seed", [(1000, 0), (5000, 1), (65536, 2)])
+def test_closest_synthetic(icp, n, seed):
+    m, p, _ = synthetic_pair(n, seed=seed)
+    idx_o, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
+    _, idx = icp.closest_matrix(p, m, return_index=True)
+    assert np.array_equal(idx, idx_o)
+
+
+def test_closest_ragged_sizes(icp):
+    rng = np.random.default_rng(11)
+    for np_, nm in [(1, 1), (3, 7), (1025, 511), (1023, 513), (2049, 64), (17, 4097)]:
+        p, m = rng.standard_normal((np_, 3)), rng.standard_normal((nm, 3))
+        idx_o, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
+        _, idx = icp.closest_matrix(p, m, return_index=True)
+        assert np.array_equal(idx, idx_o), (np_, nm)
+
+
+def test_closest_large_scale_property(icp):
+    # 2^20 points: too many for the oracle; the scene is the model itself, permuted -> idx must be the
+    # inverse permutation exactly (distance 0 is the unique minimum)
+    rng = np.random.default_rng(3)
+    n = 1 << 20
+    m = rng.uniform(-1, 1, (n, 3))
+    perm = rng.permutation(n)
+    ctx = icp.Context(0)
+    ctx.set_model(m)
+    ctx.set_scene(m[perm])
+    idx, _ = ctx.closest(want_Y=False)
+    assert np.array_equal(idx, perm.astype(np.int32))
+    st = ctx.stats()
+    assert st["nn_pairs"] == n * n
+    ctx.close()
+
+
+# ---- K2-K4 operators ------------------------------------------------------------------------------
+
+def test_find_alignment_and_err_compute(icp, clouds):
+    m, p = clouds("cow_ref"), clouds("cow_tr1")
+    ctx = icp.Context(0)
+    ctx.set_model(m)
+    ctx.set_scene(p)
+    idx, Y = ctx.closest()
+    ro = O.find_alignment(p, Y)
+    mu_p, mu_y = ctx.centroid()
+    op, oy = O.centroid(p, Y)
+    assert rel(mu_p, op) < 1e-12 and rel(mu_y, oy) < 1e-12
+    r = ctx.find_alignment()
+    assert abs(r["s"] - ro["s"]) / ro["s"] < RTOL
+    assert rel(r["R"], ro["R"]) < RTOL and rel(r["t"], ro["t"]) < RTOL
+    assert abs(r["err"] - ro["err"]) / ro["err"] < RTOL
+    # err_compute_alignment does not move the scene; err_compute does
+    assert np.array_equal(ctx.get_scene(), p)
+    e_o, newp_o = O.err_compute(p, ro["s"], ro["R"], ro["t"], Y)
+    e = ctx.err_compute(in_place=True)
+    assert abs(e - e_o) / e_o < RTOL
+    assert rel(ctx.get_scene(), newp_o) < 1e-12
+    ctx.close()
+
+
+def test_reference_shaped_wrappers(icp, clouds):
+    m, p = clouds("cow_ref"), clouds("cow_tr2")
+    idx, Y = O.closest_matrix(p, m)
+    ro = O.find_alignment(p, Y)
+    sr = ro["s"] * ro["R"]
+    e_o, newp_o = O.err_compute(p, ro["s"], ro["R"], ro["t"], Y)
+    e, newp = icp.compute_err_w(Y, p, True, sr, ro["t"])
+    assert abs(e - e_o) / e_o < RTOL and rel(newp, newp_o) < 1e-12
+    e2, same = icp.compute_err_w(Y, p, False, sr, ro["t"])
+    assert abs(e2 - O.err_compute_alignment(p, ro["s"], ro["R"], ro["t"], Y)) / e_o < RTOL
+    assert np.array_equal(same, p)
+    assert abs(icp.err_compute_alignment(p, ro["s"], ro["R"], ro["t"], Y) - e2) < 1e-9 * e2
+    mu_p, mu_y, pp, yp = O.centroid(p, Y, centred=True)
+    assert rel(icp.substract_col_w(p, mu_p), pp) < 1e-15
+    d_caps, sp = icp.y_p_norm_w(yp, pp)
+    assert abs(d_caps - (yp * yp).sum()) / (yp * yp).sum() < 1e-10
+    assert abs(sp - (pp * pp).sum()) / (pp * pp).sum() < 1e-10
+
+
+# ---- the loop ---------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("case", ["cow_tr1", "cow_tr2", "horse_tr1", "horse_tr2", "bunny"])
+def test_full_loop_matches_golden(icp, clouds, golden, case):
+    meta = json.load(open(os.path.join(GOLDEN, "meta.json")))["cases"][case]
+    g = golden(case)
+    m, p = clouds(meta["model"]), clouds(meta["scene"])
+    ctx = icp.Context(0)
+    ctx.set_model(m)
+    ctx.set_scene(p)
+    iters, err = ctx.run(meta["max_iter"], 1e-5, check_sizes=not meta["allow_unequal"])
+    assert iters == int(g["iters"])                       # identical iteration count
+    assert rel(err, g["err"]) < RTOL and np.all(np.abs(err - g["err"]) <= RTOL * np.abs(g["err"]))
+    assert np.array_equal(ctx.indices(), g["idx_last"])   # correspondences of the last iteration
+    s, R, t = ctx.transform()
+    assert abs(s - g["s"][-1]) / g["s"][-1] < RTOL and rel(R, g["R"][-1]) < RTOL
+    assert np.abs(t - g["t"][-1]).max() < RTOL * max(np.abs(g["t"][-1]).max(), np.abs(p).max() * 1e-3)
+    assert rel(ctx.get_scene(), g["new_p"]) < RTOL
+    ctx.close()
+
+
+@pytest.mark.parametrize("case", ["cow_tr1", "horse_tr2"])
+def test_per_iteration_indices_match_golden_crc(icp, clouds, golden, case):
+    # step the loop operator by operator (closest -> find_alignment -> err_compute) and compare the
+    # correspondence indices of EVERY iteration with the oracle's
+    meta = json.load(open(os.path.join(GOLDEN, "meta.json")))["cases"][case]
+    g = golden(case)
+    ctx = icp.Context(0)
+    ctx.set_model(clouds(meta["model"]))
+    ctx.set_scene(clouds(meta["scene"]))
+    n = len(clouds(meta["scene"]))
+    for i in range(int(g["iters"])):
+        idx, _ = ctx.closest(want_Y=False)
+        assert zlib.crc32(idx.tobytes()) == int(g["idx_crc"][i]), f"iteration {i}"
+        r = ctx.find_alignment()
+        err = (r["err"] + ctx.err_compute(in_place=True)) / n
+        assert abs(err - g["err"][i]) <= RTOL * g["err"][i]
+    ctx.close()
+
+
+def test_icp_class_mirrors_reference_behaviour(icp, clouds, capsys):
+    m, p = clouds("cow_ref"), clouds("cow_tr1")
+    obj = icp.ICP(m, p, 10)
+    assert obj.find_corresponding() == 7
+    err = capsys.readouterr().err.splitlines()
+    assert err[0].startswith("[ICP] iteration number 0 | error value = 0.0224295")
+    assert len(err) == 7
+    assert obj.new_p.shape == p.shape
+    with pytest.raises(SystemExit):
+        icp.ICP(m, p[:100], 3).find_corresponding()
+    assert "same number of points" in capsys.readouterr().err
+    with pytest.raises(SystemExit):
+        icp.ICP(m[:3], p[:3], 3).find_corresponding()
+    # reset + rerun gives identical results (device-side backup of the scene)
+    obj.ctx.reset_scene()
+    it2, hist2 = obj.ctx.run(10)
+    assert it2 == 7 and np.array_equal(hist2, obj.errors)

@@ -1,0 +1,103 @@
+"""CPU tests: the oracle (restatement of src/cpu.cc, src/load.cc) against the reference's only pinned
+known answer, against the committed golden vectors, and on hand-made cases."""
+import json
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, cloud_text_path, synthetic_pair
+from oracle import oracle as O
+
+
+def test_cow_runs_exactly_seven_iterations(clouds):
+    # benchmark/callgrind.out.76685:5,28306-28308: `./icp cow_ref.txt cow_tr1.txt 10` -> closest_matrix calls=7
+    m, p = clouds("cow_ref"), clouds("cow_tr1")
+    assert m.shape == (2903, 3) and p.shape == (2903, 3)     # loader drops the header: 2904 lines -> 2903 points
+    for nn_mode in (O.NN_LITERAL, O.NN_MULSQRT, O.NN_MUL):
+        for eig in (O.EIG_INTENDED, O.EIG_LITERAL):
+            r = O.icp_run(m, p, 10, nn_mode=nn_mode, eig_mode=eig)
+            assert r["iters"] == 7
+            assert r["err"][-1] < 1e-5 <= r["err"][-2]
+
+
+def test_loader_follows_load_cc(clouds, cloud_dir, tmp_path):
+    # 5-column file: sscanf("%lf,%lf,%lf") takes the first three (src/load.cc:26-28)
+    tr2 = clouds("cow_tr2")
+    assert tr2.shape == (2903, 3)
+    first = open(cloud_text_path("cow_tr2", cloud_dir)).read().splitlines()[1].split(",")
+    assert np.allclose(tr2[0], [float(x) for x in first[:3]], rtol=0, atol=0)
+    assert len(first) == 5
+    assert clouds("horse_ref").shape == (48485, 3) and clouds("bun000").shape == (40256, 3)
+    assert clouds("bun045").shape == (40097, 3)
+    with pytest.raises(FileNotFoundError):
+        O.load_matrix(str(tmp_path / "missing.txt"))
+    # no trailing newline / short file: n = lines - 1
+    f = tmp_path / "tiny.txt"
+    f.write_text("h\n1,2,3\n4,5,6")
+    assert np.array_equal(O.load_matrix(str(f)), [[1, 2, 3], [4, 5, 6]])
+
+
+def test_writer_format(tmp_path):
+    f = tmp_path / "output.txt"
+    O.write_matrix(str(f), np.array([[0.123456789, -1e-7, 1234567.0], [1, 2, 3]]))
+    assert f.read_text() == "Points_0,Points_1,Points_2\n0.123457,-1e-07,1.23457e+06\n1,2,3\n"
+
+
+def test_closest_first_minimum_on_ties():
+    m = np.array([[1.0, 0, 0], [-1.0, 0, 0], [1.0, 0, 0], [0, 5.0, 0]])
+    p = np.array([[0.0, 0, 0], [0.9, 0, 0], [0, 4.0, 0]])
+    for mode in (0, 1, 2):
+        idx, Y = O.closest_matrix(p, m, mode)
+        assert idx.tolist() == [0, 0, 3]
+        assert np.array_equal(Y, m[idx])
+
+
+def test_find_alignment_recovers_similarity():
+    rng = np.random.default_rng(1)
+    p = rng.standard_normal((50, 3))
+    a = 0.3
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
+    y = 1.7 * p @ R.T + np.array([0.3, -2.0, 5.0])
+    for eig in (O.EIG_INTENDED, O.EIG_LITERAL):
+        r = O.find_alignment(p, y, eig)
+        assert abs(r["s"] - 1.7) < 1e-12 and np.allclose(r["R"], R, atol=1e-12)
+        assert np.allclose(r["t"], [0.3, -2.0, 5.0], atol=1e-11) and r["err"] < 1e-20
+        e, newp = O.err_compute(p, r["s"], r["R"], r["t"], y)
+        assert np.allclose(newp, y, atol=1e-11) and e < 1e-20
+        assert O.err_compute_alignment(p, r["s"], r["R"], r["t"], y) == pytest.approx(r["err"], abs=1e-25)
+
+
+@pytest.mark.parametrize("case", ["cow_tr1", "cow_tr2"])
+def test_oracle_reproduces_golden(case, clouds, golden):
+    meta = json.load(open(os.path.join(GOLDEN, "meta.json")))["cases"][case]
+    g = golden(case)
+    r = O.icp_run(clouds(meta["model"]), clouds(meta["scene"]), meta["max_iter"], keep_idx=True)
+    assert r["iters"] == int(g["iters"])
+    assert np.array_equal(r["err"], g["err"])
+    assert np.array_equal(r["idx"][0], g["idx_first"]) and np.array_equal(r["idx"][-1], g["idx_last"])
+    assert [zlib.crc32(i.tobytes()) for i in r["idx"]] == g["idx_crc"].tolist()
+    assert np.array_equal(r["new_p"], g["new_p"])
+
+
+def test_golden_meta_consistency(golden):
+    meta = json.load(open(os.path.join(GOLDEN, "meta.json")))
+    assert meta["cases"]["cow_tr1"]["iters"] == 7
+    for case, info in meta["cases"].items():
+        assert info["literal_first_pass_mismatches"] == 0      # libm pow+sqrt picks the same indices as x*x
+        assert np.allclose(info["literal_eig_err_first3"], info["intended_err_first3"], rtol=1e-12)
+        assert int(golden(case)["iters"]) == info["iters"]
+
+
+def test_size_checks_mirror_alignement_check(clouds):
+    m = clouds("cow_ref")
+    assert O.icp_run(m, m[:100], 3)["iters"] == -1          # src/cpu.cc:44-47
+    assert O.icp_run(m[:3], m[:3], 3)["iters"] == -4        # src/cpu.cc:49-52
+    assert O.icp_run(m, m[:100], 1, allow_unequal=True)["iters"] == 1
+
+
+def test_synthetic_pair_has_known_correspondence():
+    m, p, perm = synthetic_pair(2000, seed=3, angle_deg=0.05, noise=1e-4, shift=(0, 0, 0))
+    idx, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
+    assert (idx == perm).mean() > 0.99
