@@ -37,13 +37,15 @@ __device__ __forceinline__ void block_sum(double (&v)[N], double* smem /* N * wa
     __syncthreads();
 }
 
+__device__ void horn_solve(const double* __restrict__ geo, const double* __restrict__ mom, double* __restrict__ xf);
+
 // ------------------------------------------------------------------------------------------------
 // K2: moments.
 __global__ void __launch_bounds__(RED_THREADS)
 moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
                const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
                const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
-               double* __restrict__ mom, int* __restrict__ ctl, int honor_done)
+               double* __restrict__ mom, int* __restrict__ ctl, int honor_done, double* __restrict__ xf_fused)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     __shared__ double red[17 * (RED_THREADS / 32)];
@@ -87,6 +89,7 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
 #pragma unroll
             for (int i = 0; i < 17; ++i) mom[1 + i] = tot[i];
             ctl[CTL_TICKET_MOM] = 0;
+            if (xf_fused) horn_solve(geo, mom, xf_fused);   // single-GPU: K3 rides on K2's last block
         }
     }
 }
@@ -130,11 +133,91 @@ __device__ void jacobi4_dev(double A[4][4], double V[4][4])
     }
 }
 
-__global__ void solve_kernel(const double* __restrict__ geo, const double* __restrict__ mom, double* __restrict__ xf,
-                             const int* __restrict__ ctl, int honor_done)
+// Fast path for the largest eigenpair of the symmetric, trace-free 4x4 matrix N:
+//   characteristic polynomial  l^4 + c2 l^2 + c1 l + c0   (c2 = -tr(N^2)/2, c1 = -tr(N^3)/3, c0 = det N),
+//   Newton from an upper bound of the spectrum (monotone convergence to the largest root because
+//   all roots are real), eigenvector = best-conditioned column of adj(N - l I).
+// Returns false when the result fails the residual test |N q - l q| <= 1e-11 |N|_F (close or
+// repeated top eigenvalues): the caller then falls back to Jacobi.
+__device__ bool top_eigenpair_fast(const double N[4][4], double upper, double q[4])
 {
-    if (honor_done && ctl[CTL_DONE]) return;
-    if (threadIdx.x != 0) return;
+    double fro2 = 0.0;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) fro2 += N[i][j] * N[i][j];
+    if (!(fro2 > 0.0)) return false;
+    const double fro = sqrt(fro2);
+    double N2[4][4];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            double a = 0.0;
+            for (int k = 0; k < 4; ++k) a += N[i][k] * N[k][j];
+            N2[i][j] = a;
+        }
+    double tr3 = 0.0;
+    for (int i = 0; i < 4; ++i)
+        for (int k = 0; k < 4; ++k) tr3 += N2[i][k] * N[k][i];
+    // det N by cofactor expansion over 2x2 minors of rows (0,1) x rows (2,3)
+    const double s0 = N[0][0] * N[1][1] - N[1][0] * N[0][1], s1 = N[0][0] * N[1][2] - N[1][0] * N[0][2];
+    const double s2 = N[0][0] * N[1][3] - N[1][0] * N[0][3], s3 = N[0][1] * N[1][2] - N[1][1] * N[0][2];
+    const double s4 = N[0][1] * N[1][3] - N[1][1] * N[0][3], s5 = N[0][2] * N[1][3] - N[1][2] * N[0][3];
+    const double t5 = N[2][2] * N[3][3] - N[3][2] * N[2][3], t4 = N[2][1] * N[3][3] - N[3][1] * N[2][3];
+    const double t3 = N[2][1] * N[3][2] - N[3][1] * N[2][2], t2 = N[2][0] * N[3][3] - N[3][0] * N[2][3];
+    const double t1 = N[2][0] * N[3][2] - N[3][0] * N[2][2], t0 = N[2][0] * N[3][1] - N[3][0] * N[2][1];
+    const double c0 = s0 * t5 - s1 * t4 + s2 * t3 + s3 * t2 - s4 * t1 + s5 * t0;
+    const double c2 = -0.5 * fro2, c1 = -tr3 / 3.0;
+    double l = fmin(fro, upper > 0.0 ? upper : fro) * (1.0 + 1e-12);
+    bool conv = false;
+    for (int it = 0; it < 64; ++it) {
+        const double l2 = l * l;
+        const double P = (l2 + c2) * l2 + c1 * l + c0;
+        const double dP = (4.0 * l2 + 2.0 * c2) * l + c1;
+        if (!(dP > 0.0)) break;
+        const double step = P / dP;
+        l -= step;
+        if (fabs(step) <= 1e-15 * fabs(l)) { conv = true; break; }
+    }
+    if (!conv) return false;
+    // adj(A), A = N - l I (symmetric).  adj = c q q^T: take the column with the largest diagonal entry.
+    double A[4][4];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) A[i][j] = N[i][j] - (i == j ? l : 0.0);
+    double adj[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            // cofactor C_ij = (-1)^(i+j) det(A without row i, col j); adj = C^T = C (symmetric)
+            const int r0 = i == 0 ? 1 : 0, r1 = i <= 1 ? 2 : 1, r2 = i <= 2 ? 3 : 2;
+            const int k0 = j == 0 ? 1 : 0, k1 = j <= 1 ? 2 : 1, k2 = j <= 2 ? 3 : 2;
+            const double d = A[r0][k0] * (A[r1][k1] * A[r2][k2] - A[r1][k2] * A[r2][k1]) -
+                             A[r0][k1] * (A[r1][k0] * A[r2][k2] - A[r1][k2] * A[r2][k0]) +
+                             A[r0][k2] * (A[r1][k0] * A[r2][k1] - A[r1][k1] * A[r2][k0]);
+            adj[i][j] = ((i + j) & 1) ? -d : d;
+        }
+    int col = 0;
+    double bestd = fabs(adj[0][0]);
+#pragma unroll
+    for (int i = 1; i < 4; ++i)
+        if (fabs(adj[i][i]) > bestd) { bestd = fabs(adj[i][i]); col = i; }
+    double v[4] = {col == 0 ? adj[0][0] : col == 1 ? adj[0][1] : col == 2 ? adj[0][2] : adj[0][3],
+                   col == 0 ? adj[1][0] : col == 1 ? adj[1][1] : col == 2 ? adj[1][2] : adj[1][3],
+                   col == 0 ? adj[2][0] : col == 1 ? adj[2][1] : col == 2 ? adj[2][2] : adj[2][3],
+                   col == 0 ? adj[3][0] : col == 1 ? adj[3][1] : col == 2 ? adj[3][2] : adj[3][3]};
+    const double nn = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
+    if (!(nn > 0.0)) return false;
+    const double inv = 1.0 / sqrt(nn);
+    double res2 = 0.0;
+    for (int i = 0; i < 4; ++i) q[i] = v[i] * inv;
+    for (int i = 0; i < 4; ++i) {
+        const double ri = N[i][0] * q[0] + N[i][1] * q[1] + N[i][2] * q[2] + N[i][3] * q[3] - l * q[i];
+        res2 += ri * ri;
+    }
+    return res2 <= 1e-22 * fro2;
+}
+
+// s, R, t from the 18 moment sums (src/cpu.cc:113-167).  Executed by ONE thread.
+__device__ void horn_solve(const double* __restrict__ geo, const double* __restrict__ mom, double* __restrict__ xf)
+{
     const double n = mom[0];
     const double mua[3] = {mom[1] / n, mom[2] / n, mom[3] / n};
     const double mub[3] = {mom[4] / n, mom[5] / n, mom[6] / n};
@@ -147,25 +230,32 @@ __global__ void solve_kernel(const double* __restrict__ geo, const double* __res
         {S[1][2] - S[2][1], S[0][0] - S[2][2] - S[1][1], S[0][1] + S[1][0], S[0][2] + S[2][0]},
         {S[2][0] - S[0][2], S[1][0] + S[0][1], S[1][1] - S[2][2] - S[0][0], S[1][2] + S[2][1]},
         {S[0][1] - S[1][0], S[2][0] + S[0][2], S[2][1] + S[1][2], S[2][2] - S[1][1] - S[0][0]}};
-    double V[4][4];
-    jacobi4_dev(N, V);
-    int kmax = 0;
-    for (int i = 1; i < 4; ++i)
-        if (N[i][i] > N[kmax][kmax]) kmax = i;
-    const double q0 = V[0][kmax], q1 = V[1][kmax], q2 = V[2][kmax], q3 = V[3][kmax];
+    const double d_caps = mom[17] - n * (mub[0] * mub[0] + mub[1] * mub[1] + mub[2] * mub[2]);
+    const double sp = mom[16] - n * (mua[0] * mua[0] + mua[1] * mua[1] + mua[2] * mua[2]);
+    double q[4];
+    if (!top_eigenpair_fast(N, 0.5 * (d_caps + sp), q)) {
+        double V[4][4];
+        jacobi4_dev(N, V);
+        int kmax = 0;
+        for (int i = 1; i < 4; ++i)
+            if (N[i][i] > N[kmax][kmax]) kmax = i;
+        for (int i = 0; i < 4; ++i) q[i] = V[i][kmax];
+    }
+    const double q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
     // R = (q_bar^T q_caps)[1:4,1:4], src/cpu.cc:138-152
     const double qb[4][4] = {{q0, -q1, -q2, -q3}, {q1, q0, q3, -q2}, {q2, -q3, q0, q1}, {q3, q2, -q1, q0}};
     const double qc[4][4] = {{q0, -q1, -q2, -q3}, {q1, q0, -q3, q2}, {q2, q3, q0, -q1}, {q3, -q2, q1, q0}};
     double R[9];
+#pragma unroll
     for (int i = 1; i < 4; ++i)
+#pragma unroll
         for (int j = 1; j < 4; ++j) {
             double acc = 0.0;
+#pragma unroll
             for (int k = 0; k < 4; ++k) acc += qb[k][i] * qc[k][j];
             R[(i - 1) * 3 + (j - 1)] = acc;
         }
     // scale and translation, src/cpu.cc:154-167
-    const double d_caps = mom[17] - n * (mub[0] * mub[0] + mub[1] * mub[1] + mub[2] * mub[2]);
-    const double sp = mom[16] - n * (mua[0] * mua[0] + mua[1] * mua[1] + mua[2] * mua[2]);
     const double s = sqrt(d_caps / sp);
     const double mup[3] = {mua[0] + geo[0], mua[1] + geo[1], mua[2] + geo[2]};
     const double muy[3] = {mub[0] + geo[0], mub[1] + geo[1], mub[2] + geo[2]};
@@ -174,6 +264,13 @@ __global__ void solve_kernel(const double* __restrict__ geo, const double* __res
     for (int a = 0; a < 3; ++a)
         xf[10 + a] = muy[a] - ((s * R[a * 3] * mup[0] + s * R[a * 3 + 1] * mup[1]) + s * R[a * 3 + 2] * mup[2]);
     for (int a = 0; a < 3; ++a) { xf[13 + a] = mup[a]; xf[16 + a] = muy[a]; }
+}
+
+__global__ void solve_kernel(const double* __restrict__ geo, const double* __restrict__ mom, double* __restrict__ xf,
+                             const int* __restrict__ ctl, int honor_done)
+{
+    if (honor_done && ctl[CTL_DONE]) return;
+    if (threadIdx.x == 0) horn_solve(geo, mom, xf);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -445,10 +542,10 @@ int reduce_blocks_for(int64_t n, int sm_count)
 }
 
 void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
-                    int honor_done, cudaStream_t st)
+                    int honor_done, double* xf_fused, cudaStream_t st)
 {
     moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
-                                                     (int)s.np, partials, mom, ctl, honor_done);
+                                                     (int)s.np, partials, mom, ctl, honor_done, xf_fused);
 }
 
 void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st)

@@ -174,7 +174,7 @@ void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1)
     if (e1) cudaEventRecord(e1, c->st);
     launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
     launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st);
-    c->stats.kernels_launched += 4;
+    c->stats.kernels_launched += 3;
 }
 
 int reset_ctl(icp_ctx* c)
@@ -424,7 +424,7 @@ int icp_centroid(icp_ctx* c, double mu_p[3], double mu_y[3])
     int r;
     if ((r = need_idx(c, "icp_centroid"))) return r;
     CK(cudaSetDevice(c->device));
-    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->st);
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, nullptr, c->st);
     if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
     launch_centroid_export(c->m, c->d_mom, c->d_out6, c->st);
     double h[6];
@@ -453,9 +453,11 @@ int icp_find_alignment(icp_ctx* c, double* s, double R[9], double t[3], double* 
     int r;
     if ((r = need_idx(c, "icp_find_alignment"))) return r;
     CK(cudaSetDevice(c->device));
-    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->st);
-    if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
-    launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 0, c->st);
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->comm ? nullptr : c->d_xf, c->st);
+    if (c->comm) {
+        if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+        launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 0, c->st);
+    }
     launch_transform(c->m, c->s, c->d_xf, 0, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 0, 0, 1.0, 0.0,
                      nullptr, c->st);
     if ((r = allreduce(c, c->d_err_sum, 1))) return r;
@@ -518,12 +520,16 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     CK(cudaEventRecord(c->ev0, c->st));
     for (int it = 0; it < max_iter; ++it) {
         nn_pass(c, 1, c->ev_filter[2 * it], c->ev_filter[2 * it + 1]);
-        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, c->st);
-        if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
-        launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
+        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, c->comm ? nullptr : c->d_xf,
+                       c->st);
+        if (c->comm) {
+            if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+            launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
+            c->stats.kernels_launched += 1;
+        }
         launch_transform(c->m, c->s, c->d_xf, 1, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 1,
                          c->comm ? 0 : 1, np_glob, threshold, c->d_err_hist, c->st);
-        c->stats.kernels_launched += 3;
+        c->stats.kernels_launched += 2;
         if (c->comm) {
             if ((r = allreduce(c, c->d_err_sum, 1))) return r;
             launch_finish(c->d_err_sum, np_glob, threshold, c->d_err_hist, c->d_ctl, c->st);
@@ -646,7 +652,7 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
     icp_ctx* c = nullptr;
     int r = pair_ctx(&c, y_xyz, p_xyz, n);
     if (r) return r;
-    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->st);
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, nullptr, c->st);
     double mom[MOM_N], geo[4];
     cudaError_t e = cudaMemcpyAsync(mom, c->d_mom, sizeof(mom), cudaMemcpyDeviceToHost, c->st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(geo, c->m.geo, sizeof(geo), cudaMemcpyDeviceToHost, c->st);

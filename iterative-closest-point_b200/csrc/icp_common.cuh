@@ -30,7 +30,7 @@ constexpr int XF_N  = 20;   // s, R[9], t[3], mu_p[3], mu_y[3], spare
 
 // ctl[] slots (int32, device)
 enum { CTL_DONE = 0, CTL_ITERS = 1, CTL_AMB_COUNT = 2, CTL_TICKET_MOM = 3, CTL_TICKET_ERR = 4,
-       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_N = 8 };
+       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_TICKET_NN = 7, CTL_N = 8 };
 
 struct ModelDev {
     int64_t nm = 0, nm_pad = 0;
@@ -68,8 +68,9 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                      int sm_count, cudaStream_t st);
 
+// xf_fused != nullptr: the last block also runs the Horn solve (K3) into xf_fused (single-GPU path).
 void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
-                    int honor_done, cudaStream_t st);
+                    int honor_done, double* xf_fused, cudaStream_t st);
 void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st);
 // in_place: p <- sR p + t (FP64 master and FP32 shadow).  finish: the last block also closes the iteration
 // (err_hist[it] = 2*sum/n, done flag, iteration counter) — single-GPU loop only.

@@ -205,26 +205,45 @@ nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx,
 }
 
 // ------------------------------------------------------------------------------------------------
-// The reference's distance expression, FP64, no contraction (src/cpu.cc:16-19 with pow(x,2) == x*x).
-__device__ __forceinline__ double dist64(double px, double py, double pz, double mx, double my, double mz)
+// The reference's distance expression, FP64, no contraction (src/cpu.cc:16-19 with pow(x,2) == x*x):
+// the squared sum; the sqrt is applied lazily (see Best64).
+__device__ __forceinline__ double dist2_64(double px, double py, double pz, double mx, double my, double mz)
 {
     const double dx = __dsub_rn(px, mx), dy = __dsub_rn(py, my), dz = __dsub_rn(pz, mz);
-    const double s = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-    return __dsqrt_rn(s);
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
-// lexicographic (value, index) minimum across the warp: lowest index wins ties
-__device__ __forceinline__ void warp_argmin(double& v, int& k)
+// Running first-minimum of v = sqrt(s) over ascending indices, exactly as Eigen's minCoeff sees the
+// reference's d(k) = sqrt(...) (src/cpu.cc:19-22), but evaluating the sqrt only when s improves:
+// sqrt is monotone, so s >= s_best can never give a strictly smaller v.
+struct Best64 {
+    double s, v;
+    int k;
+    __device__ __forceinline__ void init() { s = v = __longlong_as_double(0x7ff0000000000000LL); k = 0x7fffffff; }
+    __device__ __forceinline__ void feed(double s_new, int k_new)   // k_new > k of everything fed before
+    {
+        if (s_new < s) {
+            const double v_new = __dsqrt_rn(s_new);
+            if (v_new < v) { v = v_new; k = k_new; }
+            s = s_new;   // equal sqrt: the earlier index stays, the smaller s keeps filtering
+        }
+    }
+};
+
+// lexicographic (value, index) minimum over `width` adjacent lanes: lowest index wins ties
+template <int WIDTH>
+__device__ __forceinline__ void group_argmin(double& v, int& k, unsigned mask = 0xffffffffu)
 {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const double ov = __shfl_xor_sync(0xffffffffu, v, o);
-        const int ok = __shfl_xor_sync(0xffffffffu, k, o);
+    for (int o = WIDTH / 2; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(mask, v, o);
+        const int ok = __shfl_xor_sync(mask, k, o);
         if (ov < v || (ov == v && ok < k)) { v = ov; k = ok; }
     }
 }
 
 constexpr int REFINE_THREADS = 256;
+constexpr int RF = 8;    // lanes cooperating on one scene point
 
 __global__ void __launch_bounds__(REFINE_THREADS)
 nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
@@ -236,42 +255,39 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
                  int* __restrict__ ctl, int honor_done)
 {
     if (honor_done && ctl[CTL_DONE]) return;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, sub = lane & (RF - 1), grp = lane / RF;
     const int warp = (blockIdx.x * REFINE_THREADS + threadIdx.x) >> 5;
     const int n_warps = (gridDim.x * REFINE_THREADS) >> 5;
+    constexpr int PPW = 32 / RF;                       // scene points per warp
     const double Rm = geo[3];
     const float INF = __int_as_float(0x7f800000);
 
-    for (int j = warp; j < np; j += n_warps) {
-        // ---- merge the model splits (lanes parallel over splits, 32 at a time) ---------------------
-        float best = INF, runner = INF;
-        uint32_t chunk = 0;
-        for (int s0 = 0; s0 < n_splits; s0 += 32) {
-            const int s = s0 + lane;
-            float b = INF, rn = INF;
-            uint32_t ch = 0;
-            if (s < n_splits) {
-                const size_t o = (size_t)s * np_pad + j;
-                b = part_best[o]; rn = part_runner[o]; ch = part_chunk[o];
-            }
-            float gb = b;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) gb = fminf(gb, __shfl_xor_sync(0xffffffffu, gb, o));
-            const unsigned eq = __ballot_sync(0xffffffffu, b == gb);
-            const int src = __ffs(eq) - 1;
-            float others = (lane == src) ? rn : b;       // runner-up candidates of this group
-            if (__popc(eq) > 1 && gb < INF) others = gb; // equal minima in two splits: ambiguous
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) others = fminf(others, __shfl_xor_sync(0xffffffffu, others, o));
-            const uint32_t gch = __shfl_sync(0xffffffffu, ch, src);
-            // fold group result into the running (best, runner, chunk)
-            if (gb < best) { runner = fminf(fminf(runner, best), others); best = gb; chunk = gch; }
-            else           { runner = fminf(runner, fminf(others, gb)); }
+    for (int jb = warp * PPW; jb < np; jb += n_warps * PPW) {
+        const bool valid = jb + grp < np;
+        const int j = valid ? jb + grp : np - 1;
+        // ---- merge the model splits (RF lanes stride over the splits) ------------------------------
+        float b = INF, rn = INF;
+        uint32_t ch = 0;
+        for (int s = sub; s < n_splits; s += RF) {
+            const size_t o = (size_t)s * np_pad + j;
+            const float sb = part_best[o], sr = part_runner[o];
+            const uint32_t sc = part_chunk[o];
+            if (sb < b) { rn = fminf(fminf(rn, b), sr); b = sb; ch = sc; }
+            else        { rn = fminf(rn, fminf(sr, sb)); }     // sb == b: tie -> runner = best -> ambiguous
         }
+        float best = b;
+#pragma unroll
+        for (int o = RF / 2; o > 0; o >>= 1) best = fminf(best, __shfl_xor_sync(0xffffffffu, best, o));
+        const unsigned eq = (__ballot_sync(0xffffffffu, b == best) >> (grp * RF)) & ((1u << RF) - 1u);
+        const int src = __ffs(eq) - 1;
+        float runner = (sub == src) ? rn : b;
+        if (__popc(eq) > 1 && best < INF) runner = best;
+#pragma unroll
+        for (int o = RF / 2; o > 0; o >>= 1) runner = fminf(runner, __shfl_xor_sync(0xffffffffu, runner, o));
+        const uint32_t chunk = __shfl_sync(0xffffffffu, ch, grp * RF + src);
 
         // ---- rigorous FP32 error bound ------------------------------------------------------------
-        const int tile = j / NN_TILE;
-        const int cj = tile * NN_TILE + NN_TILE / 2;
+        const int cj = (j / NN_TILE) * NN_TILE + NN_TILE / 2;
         const float hx = phx[j], hy = phy[j], hz = phz[j];
         const float lx = __fsub_rn(hx, phx[cj]), ly = __fsub_rn(hy, phy[cj]), lz = __fsub_rn(hz, phz[cj]);
         const double P2 = (double)lx * lx + (double)ly * ly + (double)lz * lz;
@@ -293,33 +309,39 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
             // ---- FP64 re-rank of the best chunk with the reference's expression -------------------
             const double px = p64x[j], py = p64y[j], pz = p64z[j];
             const int k0 = (int)chunk * NN_G;
-            double v = __longlong_as_double(0x7ff0000000000000LL);
-            int k = 0x7fffffff;
+            double s2[NN_G / RF];
 #pragma unroll
-            for (int i = 0; i < NN_G / 32; ++i) {
-                const int kk = k0 + i * 32 + lane;
-                if (kk < nm) {
-                    const double d = dist64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]);
-                    if (d < v) { v = d; k = kk; }
-                }
+            for (int i = 0; i < NN_G / RF; ++i) {
+                const int kk = min(k0 + i * RF + sub, nm - 1);
+                s2[i] = dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]);
             }
-            warp_argmin(v, k);
-            if (lane == 0) idx[j] = k;
-        } else if (lane == 0) {
+            Best64 bt;
+            bt.init();
+#pragma unroll
+            for (int i = 0; i < NN_G / RF; ++i) {
+                const int kk = k0 + i * RF + sub;
+                if (kk < nm) bt.feed(s2[i], kk);
+            }
+            double v = bt.v;
+            int k = bt.k;
+            group_argmin<RF>(v, k, ((1u << RF) - 1u) << (grp * RF));   // `clear` is uniform per group, not per warp
+            if (sub == 0 && valid) idx[j] = k;
+        } else if (sub == 0 && valid) {
             const int pos = atomicAdd(&ctl[CTL_AMB_COUNT], 1);
             amb_list[pos] = j;
         }
     }
 }
 
-// Full FP64 scan for the scene points the filter could not decide.  One CTA per queued point.
+// Full FP64 scan for the scene points the filter could not decide.  One CTA per queued point; the
+// last CTA to finish folds the pass's counters into the totals.
 constexpr int EXACT_THREADS = 256;
 
 __global__ void __launch_bounds__(EXACT_THREADS)
 nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
                 int nm, const double* __restrict__ p64x, const double* __restrict__ p64y,
                 const double* __restrict__ p64z, const int32_t* __restrict__ amb_list, int32_t* __restrict__ idx,
-                const int* __restrict__ ctl, int honor_done)
+                int* __restrict__ ctl, int np, int honor_done)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     __shared__ double sv[EXACT_THREADS / 32];
@@ -329,33 +351,39 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
     for (int a = blockIdx.x; a < count; a += gridDim.x) {
         const int j = amb_list[a];
         const double px = p64x[j], py = p64y[j], pz = p64z[j];
-        double v = __longlong_as_double(0x7ff0000000000000LL);
-        int k = 0x7fffffff;
-        for (int kk = threadIdx.x; kk < nm; kk += EXACT_THREADS) {
-            const double d = dist64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]);
-            if (d < v) { v = d; k = kk; }   // ascending kk per thread: first minimum kept
+        Best64 bt;
+        bt.init();
+        int kk = threadIdx.x;
+        for (; kk + 3 * EXACT_THREADS < nm; kk += 4 * EXACT_THREADS) {    // 4 independent evaluations in flight
+            const double s0 = dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]);
+            const double s1 = dist2_64(px, py, pz, m64x[kk + EXACT_THREADS], m64y[kk + EXACT_THREADS], m64z[kk + EXACT_THREADS]);
+            const double s2 = dist2_64(px, py, pz, m64x[kk + 2 * EXACT_THREADS], m64y[kk + 2 * EXACT_THREADS], m64z[kk + 2 * EXACT_THREADS]);
+            const double s3 = dist2_64(px, py, pz, m64x[kk + 3 * EXACT_THREADS], m64y[kk + 3 * EXACT_THREADS], m64z[kk + 3 * EXACT_THREADS]);
+            bt.feed(s0, kk); bt.feed(s1, kk + EXACT_THREADS); bt.feed(s2, kk + 2 * EXACT_THREADS); bt.feed(s3, kk + 3 * EXACT_THREADS);
         }
-        warp_argmin(v, k);
+        for (; kk < nm; kk += EXACT_THREADS) bt.feed(dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]), kk);
+        double v = bt.v;
+        int k = bt.k;
+        group_argmin<32>(v, k);
         if (lane == 0) { sv[w] = v; sk[w] = k; }
         __syncthreads();
         if (w == 0) {
             v = lane < EXACT_THREADS / 32 ? sv[lane] : __longlong_as_double(0x7ff0000000000000LL);
             k = lane < EXACT_THREADS / 32 ? sk[lane] : 0x7fffffff;
-            warp_argmin(v, k);
+            group_argmin<32>(v, k);
             if (lane == 0) idx[j] = k;
         }
         __syncthreads();
     }
-}
-
-// Bookkeeping after the exact pass: fold the per-pass ambiguous count into the totals, reset it.
-__global__ void nn_account_kernel(int* ctl, int np, int honor_done)
-{
-    if (honor_done && ctl[CTL_DONE]) return;
-    const int amb = ctl[CTL_AMB_COUNT];
-    ctl[CTL_AMB_TOTAL] += amb;
-    ctl[CTL_CHUNK_TOTAL] += np - amb;
-    ctl[CTL_AMB_COUNT] = 0;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&ctl[CTL_TICKET_NN], 1) == (int)gridDim.x - 1) {
+            ctl[CTL_AMB_TOTAL] += count;
+            ctl[CTL_CHUNK_TOTAL] += np - count;
+            ctl[CTL_AMB_COUNT] = 0;
+            ctl[CTL_TICKET_NN] = 0;
+        }
+    }
 }
 
 }  // namespace
@@ -379,7 +407,7 @@ void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
 void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                       cudaStream_t st)
 {
-    const int64_t warps = s.np;
+    const int64_t warps = (s.np + 32 / RF - 1) / (32 / RF);
     int grid = (int)((warps * 32 + REFINE_THREADS - 1) / REFINE_THREADS);
     if (grid > 148 * 16) grid = 148 * 16;
     if (grid < 1) grid = 1;
@@ -396,8 +424,7 @@ void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, 
     if ((int64_t)grid > s.np) grid = (int)s.np;
     if (grid < 1) grid = 1;
     nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, (int)m.nm, s.p64x, s.p64y, s.p64z,
-                                                    sc.amb_list, s.idx, ctl, honor_done);
-    nn_account_kernel<<<1, 1, 0, st>>>(ctl, (int)s.np, honor_done);
+                                                    sc.amb_list, s.idx, ctl, (int)s.np, honor_done);
 }
 
 }  // namespace icpb

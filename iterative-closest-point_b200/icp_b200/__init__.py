@@ -215,6 +215,18 @@ class Context:
         _ck(self._L.icp_comm_init(self._h, path.encode() if path else None, buf, int(rank), int(world)))
 
 
+def shard_range(n, rank, world):
+    """Contiguous block of scene points held by `rank` (scene sharded, model replicated)."""
+    base, rem = divmod(int(n), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+# Layout of the per-iteration exchange (csrc/icp_common.cuh MOM_N): all-reduced with SUM.
+MOMENT_FIELDS = ("n", "sum_a[3]", "sum_b[3]", "sum_abT[9]", "sum_aa", "sum_bb")   # a = p - c0, b = y - c0
+MOMENT_DOUBLES = 18
+
+
 def comm_unique_id(nccl_path=None):
     path = nccl_path or torch_nccl_path()
     buf = C.create_string_buffer(128)

@@ -1,0 +1,59 @@
+"""GPU test of the `icp [ref] [scene] [nb_max_iter]` driver (reference src/main.cc:5-25): same stdout /
+stderr text, same output.txt bytes as the oracle's restatement of the reference's loader, loop and writer."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import PKG_DIR, cloud_text_path
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+ICP_BIN = os.path.join(PKG_DIR, "bin", "icp")
+
+
+def run_icp(args, cwd, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run([ICP_BIN] + args, cwd=str(cwd), capture_output=True, text=True, timeout=300, env=e)
+
+
+def test_usage_and_missing_file(tmp_path):
+    r = run_icp([], tmp_path)
+    assert r.returncode == 255 and r.stdout == "Usage: ./icp [path_to_ref_cloud] [path_to_transform_cloud] [nb_iter]\n"
+    r = run_icp(["nope.txt", "nope2.txt", "3"], tmp_path)
+    assert r.returncode == 2                                    # src/load.cc:11-14
+    assert "[load] opening nope.txt" in r.stderr and "could not be opened" in r.stderr
+
+
+def test_cow_end_to_end(tmp_path, cloud_dir):
+    ref, scene = cloud_text_path("cow_ref", cloud_dir), cloud_text_path("cow_tr1", cloud_dir)
+    r = run_icp([ref, scene, "10"], tmp_path)
+    assert r.returncode == 0, r.stderr
+    lines = r.stderr.splitlines()
+    assert lines[0] == f"[load] opening {ref}" and lines[1] == "[load] loading file into matrix"
+    it_lines = [l for l in lines if l.startswith("[ICP] iteration number")]
+    ro = O.icp_run(O.load_matrix(ref), O.load_matrix(scene), 10)
+    assert len(it_lines) == ro["iters"] == 7                     # the reference's pinned known answer
+    for i, l in enumerate(it_lines):
+        assert l.startswith(f"[ICP] iteration number {i} | error value = ")
+        assert abs(float(l.split("=")[1]) - ro["err"][i]) <= 2e-5 * ro["err"][i]   # 6 significant digits printed
+    assert lines[-1] == '[output] output file "output.txt" was generated.'
+    O.write_matrix(str(tmp_path / "oracle_output.txt"), ro["new_p"])
+    got = (tmp_path / "output.txt").read_text().splitlines()
+    want = (tmp_path / "oracle_output.txt").read_text().splitlines()
+    assert got[0] == want[0] == "Points_0,Points_1,Points_2" and len(got) == len(want) == 2904
+    g = np.array([[float(x) for x in l.split(",")] for l in got[1:]])
+    w = np.array([[float(x) for x in l.split(",")] for l in want[1:]])
+    assert np.abs(g - w).max() <= 1e-5 * np.abs(w).max()
+    assert sum(a != b for a, b in zip(got, want)) <= 5             # 6-digit text: identical but for rounding flips
+
+
+def test_size_mismatch_exits_like_reference(tmp_path, cloud_dir):
+    ref, scene = cloud_text_path("bun000", cloud_dir), cloud_text_path("bun045", cloud_dir)
+    r = run_icp([ref, scene, "2"], tmp_path)
+    assert r.returncode == 255                                   # exit(-1), src/cpu.cc:44-47
+    assert "[error] Point sets need to have the same number of points." in r.stderr
+    r = run_icp([ref, scene, "2"], tmp_path, env={"ICP_ALLOW_UNEQUAL": "1"})
+    assert r.returncode == 0 and r.stderr.count("[ICP] iteration number") == 2

@@ -215,3 +215,53 @@ def test_icp_class_mirrors_reference_behaviour(icp, clouds, capsys):
     obj.ctx.reset_scene()
     it2, hist2 = obj.ctx.run(10)
     assert it2 == 7 and np.array_equal(hist2, obj.errors)
+
+
+# ---- K3 robustness: fast quartic/adjugate path and its Jacobi fallback -------------------------------
+
+def _align_via_gpu(icp, p, y):
+    """find_alignment on explicit pairs (model = y, correspondence forced by making y_j nearest to p_j)."""
+    ctx = icp.Context(0)
+    ctx.set_model(y)
+    ctx.set_scene(p)
+    idx, _ = ctx.closest(want_Y=False)
+    r = ctx.find_alignment()
+    ctx.close()
+    return idx, r
+
+
+@pytest.mark.parametrize("kind", ["generic", "identity", "planar", "scaled", "big_rotation", "tiny", "far_from_origin"])
+def test_horn_solver_cases(icp, kind):
+    rng = np.random.default_rng(42)
+    n = 500
+    y = rng.standard_normal((n, 3))
+    a = {"big_rotation": 2.9}.get(kind, 0.02)
+    ax = np.array([0.3, -0.5, 0.81]); ax /= np.linalg.norm(ax)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
+    s, t = 1.0, np.array([0.01, -0.02, 0.005])
+    if kind == "identity":
+        R, t = np.eye(3), np.zeros(3)
+    if kind == "planar":
+        y[:, 2] = 0.0
+    if kind == "scaled":
+        s = 1.02
+    if kind == "tiny":
+        y *= 1e-4; t *= 1e-4
+    if kind == "far_from_origin":
+        y += 1000.0
+    # scene = inverse transform of the model, so that the alignment p -> y is (s, R, t)
+    p = ((y - t) / s) @ R                     # p_j = R^T (y_j - t) / s
+    if kind == "big_rotation":
+        idx = np.arange(n)                    # NN would not pair them; use the operator-level wrapper instead
+        ro = O.find_alignment(p, y)
+        e, _ = icp.compute_err_w(y, p, False, ro["s"] * ro["R"], ro["t"])
+        assert e < 1e-18 * max(1.0, np.abs(y).max() ** 2) * n
+        return
+    idx, r = _align_via_gpu(icp, p, y)
+    assert np.array_equal(idx, np.arange(n))
+    ro = O.find_alignment(p, y)
+    assert abs(r["s"] - ro["s"]) < 1e-9 * ro["s"]
+    assert np.abs(r["R"] - ro["R"]).max() < 1e-8
+    assert np.abs(r["t"] - ro["t"]).max() < 1e-8 * max(1.0, np.abs(y).max())
+    assert np.abs(r["R"] - R).max() < 1e-7 and abs(r["s"] - s) < 1e-9
