@@ -113,12 +113,15 @@ int icp_get_stats(icp_ctx* ctx, icp_stats* out);
  * wrappers of src/GPU/gpu.hh:110-116; each creates and destroys a context on device 0.
  * icp_closest_matrix_host   compute_Y_w_opti / CPU::closest_matrix
  * icp_nearest_index_host    compute_distance_w_naive(m, pi) -> int     src/GPU/compute.cu:279-308
+ * icp_find_alignment_host   ICP::find_alignment(Y) on explicit pairs    src/cpu.cc:105-175, src/GPU/gpu.cc:95-151
  * icp_err_compute_host      compute_err_w(Y, p, in_place, sr, t)        src/GPU/compute.cu:348-379
  * icp_subtract_col_host     substract_col_w(M, m)                       src/GPU/compute.cu:400-416
  * icp_y_p_norm_host         y_p_norm_w(y, p, n, d_caps, sp)             src/GPU/compute.cu:442-469 */
 int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np,
                             int32_t* idx_out, double* Y_xyz_out);
 int icp_nearest_index_host(const double* m_xyz, int64_t nm, const double pi[3], int32_t* idx_out);
+int icp_find_alignment_host(const double* Y_xyz, const double* p_xyz, int64_t np, double* s, double R[9],
+                            double t[3], double* err_align);
 int icp_err_compute_host(const double* Y_xyz, double* p_xyz, int64_t np, int in_place,
                          const double sr[9], const double t[3], double* err);
 int icp_subtract_col_host(const double* M_xyz, int64_t n, const double m[3], double* out_xyz);

@@ -630,6 +630,18 @@ int icp_err_compute_host(const double* Y_xyz, double* p_xyz, int64_t np, int in_
     return r;
 }
 
+int icp_find_alignment_host(const double* Y_xyz, const double* p_xyz, int64_t np, double* s, double R[9], double t[3],
+                            double* err_align)
+{
+    if (!Y_xyz || !p_xyz || np < 1) { g_err = "icp_find_alignment_host: bad arguments"; return ICP_ERR_INVALID; }
+    icp_ctx* c = nullptr;
+    int r = pair_ctx(&c, Y_xyz, p_xyz, np);
+    if (r) return r;
+    r = icp_find_alignment(c, s, R, t, err_align);
+    icp_destroy(c);
+    return r;
+}
+
 int icp_subtract_col_host(const double* M_xyz, int64_t n, const double m[3], double* out_xyz)
 {
     if (!M_xyz || !m || !out_xyz || n < 1) { g_err = "icp_subtract_col_host: bad arguments"; return ICP_ERR_INVALID; }

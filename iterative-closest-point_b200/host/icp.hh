@@ -176,15 +176,13 @@ public:
         return Y;
     }
 
-    // src/cpu.cc:105-175.  `y` must be the correspondences of the current new_p (as in the reference's
-    // loop); they are recomputed on the device rather than re-uploaded.
-    double find_alignment(const Matrix& /*y*/)
+    // src/cpu.cc:105-175: s, R, t from new_p and the given correspondences y; returns err_compute_alignment.
+    double find_alignment(const Matrix& y)
     {
-        int rc = icp_closest(ctx, nullptr, nullptr);
-        if (rc) die("icp_closest", rc);
-        double sr_[9], t_[3], err = 0.0;
-        if ((rc = icp_find_alignment(ctx, &s, sr_, t_, &err))) die("icp_find_alignment", rc);
-        r = from_rowmajor3(sr_);
+        double R_[9], t_[3], err = 0.0;
+        int rc = icp_find_alignment_host(y.data(), new_p.data(), np, &s, R_, t_, &err);
+        if (rc) die("icp_find_alignment_host", rc);
+        r = from_rowmajor3(R_);
         for (int i = 0; i < 3; ++i) t(i) = t_[i];
         return err;
     }

@@ -30,7 +30,7 @@ EXPORTS = [
     "icp_create", "icp_destroy", "icp_last_error", "icp_version", "icp_set_model", "icp_set_scene",
     "icp_get_scene", "icp_reset_scene", "icp_closest", "icp_centroid", "icp_find_alignment", "icp_err_compute",
     "icp_get_transform", "icp_run", "icp_get_indices", "icp_get_stats", "icp_closest_matrix_host",
-    "icp_nearest_index_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
+    "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
     "icp_comm_unique_id", "icp_comm_init", "icp_comm_world",
 ]
 
@@ -86,6 +86,7 @@ def load_library(path=None):
     L.icp_get_stats.argtypes = [vp, C.POINTER(IcpStats)]
     L.icp_closest_matrix_host.argtypes = [_dp, C.c_int64, _dp, C.c_int64, _ip, _dp]
     L.icp_nearest_index_host.argtypes = [_dp, C.c_int64, _dp, _ip]
+    L.icp_find_alignment_host.argtypes = [_dp, _dp, C.c_int64, _dp, _dp, _dp, _dp]
     L.icp_err_compute_host.argtypes = [_dp, _dp, C.c_int64, C.c_int, _dp, _dp, _dp]
     L.icp_subtract_col_host.argtypes = [_dp, C.c_int64, _dp, _dp]
     L.icp_y_p_norm_host.argtypes = [_dp, _dp, C.c_int64, _dp, _dp]
@@ -265,6 +266,14 @@ def compute_err_w(Y, p, in_place, sr, t):
     e = C.c_double()
     _ck(load_library().icp_err_compute_host(_d(Y), _d(p), len(p), int(bool(in_place)), _d(sr), _d(t), C.byref(e)))
     return e.value, p
+
+
+def find_alignment(p, y):
+    """ICP::find_alignment(Y) on explicit pairs (src/cpu.cc:105-175) -> dict(s, R, t, err)."""
+    p, y = _pts(p), _pts(y)
+    s = C.c_double(); e = C.c_double(); R = np.empty(9); t = np.empty(3)
+    _ck(load_library().icp_find_alignment_host(_d(y), _d(p), len(p), C.byref(s), _d(R), _d(t), C.byref(e)))
+    return dict(s=s.value, R=R.reshape(3, 3), t=t, err=e.value)
 
 
 def err_compute(p, s, R, t, Y):

@@ -219,18 +219,7 @@ def test_icp_class_mirrors_reference_behaviour(icp, clouds, capsys):
 
 # ---- K3 robustness: fast quartic/adjugate path and its Jacobi fallback -------------------------------
 
-def _align_via_gpu(icp, p, y):
-    """find_alignment on explicit pairs (model = y, correspondence forced by making y_j nearest to p_j)."""
-    ctx = icp.Context(0)
-    ctx.set_model(y)
-    ctx.set_scene(p)
-    idx, _ = ctx.closest(want_Y=False)
-    r = ctx.find_alignment()
-    ctx.close()
-    return idx, r
-
-
-@pytest.mark.parametrize("kind", ["generic", "identity", "planar", "scaled", "big_rotation", "tiny", "far_from_origin"])
+@pytest.mark.parametrize("kind", ["generic", "identity", "planar", "collinear", "scaled", "big_rotation", "tiny", "far_from_origin"])
 def test_horn_solver_cases(icp, kind):
     rng = np.random.default_rng(42)
     n = 500
@@ -244,6 +233,8 @@ def test_horn_solver_cases(icp, kind):
         R, t = np.eye(3), np.zeros(3)
     if kind == "planar":
         y[:, 2] = 0.0
+    if kind == "collinear":                   # rotation about the line is undetermined: only the residual is checked
+        y = np.outer(rng.standard_normal(n), [1.0, 2.0, -0.5])
     if kind == "scaled":
         s = 1.02
     if kind == "tiny":
@@ -252,16 +243,12 @@ def test_horn_solver_cases(icp, kind):
         y += 1000.0
     # scene = inverse transform of the model, so that the alignment p -> y is (s, R, t)
     p = ((y - t) / s) @ R                     # p_j = R^T (y_j - t) / s
-    if kind == "big_rotation":
-        idx = np.arange(n)                    # NN would not pair them; use the operator-level wrapper instead
-        ro = O.find_alignment(p, y)
-        e, _ = icp.compute_err_w(y, p, False, ro["s"] * ro["R"], ro["t"])
-        assert e < 1e-18 * max(1.0, np.abs(y).max() ** 2) * n
-        return
-    idx, r = _align_via_gpu(icp, p, y)
-    assert np.array_equal(idx, np.arange(n))
+    r = icp.find_alignment(p, y)          # K2 + K3 + K4 on explicit pairs
     ro = O.find_alignment(p, y)
     assert abs(r["s"] - ro["s"]) < 1e-9 * ro["s"]
+    assert r["err"] <= 1e-18 * n * max(1.0, np.abs(y).max() ** 2) + 1e-9 * abs(ro["err"])
+    if kind == "collinear":
+        return
     assert np.abs(r["R"] - ro["R"]).max() < 1e-8
     assert np.abs(r["t"] - ro["t"]).max() < 1e-8 * max(1.0, np.abs(y).max())
     assert np.abs(r["R"] - R).max() < 1e-7 and abs(r["s"] - s) < 1e-9
