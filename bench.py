@@ -80,7 +80,7 @@ class ClockSampler:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -117,6 +117,14 @@ def fp32_peak_tflops():
     return 148 * 128 * 2 * mhz * 1e6 / 1e12, src
 
 
+def host_threads():
+    """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1, which is not what we want)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def cpu_port_throughput(m, p, iters, threads=0):
     """Times the oracle's loop (restated src/cpu.cc:55-79, x*x + sqrt distance form) -> evals/s."""
     from oracle import oracle as O
@@ -138,7 +146,7 @@ def run_reference(args, rank, world):
         sample_iters = 1
     vals = []
     for i in range(args.warmup + args.steps):
-        v, it, dt, cores = cpu_port_throughput(m, p, sample_iters)
+        v, it, dt, cores = cpu_port_throughput(m, p, sample_iters, threads=host_threads())
         if i >= args.warmup:
             vals.append((v, it, dt))
     value = float(np.mean([v for v, _, _ in vals]))
@@ -169,11 +177,25 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         check = False        # global scene = `world` shards of np points; the model stays nm points
 
+    if world > 1 and args.scaling == "strong":      # one global scene, contiguous block per rank
+        lo, hi = icp_b200.shard_range(len(p), rank, world)
+        p_global_n = len(p)
+        p = np.ascontiguousarray(p[lo:hi])
+    else:
+        p_global_n = len(p) * world
     ctx = icp_b200.Context(local_rank)
+    comm_kind = "none"
     if world > 1:
         uid = [icp_b200.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         ctx.comm_init(uid[0], rank, world)
+        comm_kind = "nccl all-reduce of 18+1 doubles per iteration"
+        if os.environ.get("ICP_COMM", "peer") != "nccl":
+            handles = [None] * world
+            dist.all_gather_object(handles, ctx.comm_peer_handle())
+            ctx.comm_peer_attach(handles, rank, world)
+            dist.barrier()
+            comm_kind = "in-kernel peer-mailbox exchange of 18+1 doubles per iteration over NVLink (no collective launch)"
     ctx.set_model(m)
     ctx.set_scene(p)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
@@ -232,7 +254,7 @@ def run_ours(args, rank, world, local_rank):
             dist.destroy_process_group()
         return
 
-    pairs_per_iter = len(m) * len(p) * world
+    pairs_per_iter = len(m) * p_global_n
     evals = pairs_per_iter * (iters_total / args.steps)
     ms_per_step = dev_ms / args.steps
     value = evals / (ms_per_step * 1e-3)
@@ -244,27 +266,31 @@ def run_ours(args, rank, world, local_rank):
         traffic = json.load(open(os.path.join(ROOT, "profiles", "nn_filter_traffic.json")))
     except Exception:
         pass
-    cpu_iters = 8 if len(m) * len(p) < 5e9 else 1
-    pc = p if len(m) * len(p) < 1e11 else p[:4096]
-    cv, cit, cdt, cores = cpu_port_throughput(m, pc, cpu_iters)
+    cpu = None
+    if world == 1:      # the CPU baseline is reported at N = 1 only
+        cpu_iters = 8 if len(m) * len(p) < 5e9 else 1
+        pc = p if len(m) * len(p) < 1e11 else p[:4096]
+        cv, cit, cdt, cores = cpu_port_throughput(m, pc, cpu_iters, threads=host_threads())
+        cpu = {"value": cv, "unit": "evals/s", "cores": cores, "kind": "port",
+               "sample": f"{cit} ICP iteration(s), {len(pc)} scene x {len(m)} model points, oracle x*x+sqrt form"}
     line = {
         "metric": "nn_distance_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": args.scaling if world > 1 else "weak",
         "vs_baseline": None, "dtype": "f32 filter + f64 re-rank/alignment",
         "data": "reference clouds (tests/golden/clouds)" if args.workload in WORKLOADS else "synthetic",
         "icp_iterations_per_sec": (iters_total / args.steps) / (ms_per_step * 1e-3),
         "iterations_per_step": iters_total / args.steps, "final_error_value": float(hist[-1]),
         "config": {"workload": args.workload, "description": desc, "np_per_gpu": len(p), "nm": len(m),
-                   "sharding": "1 GPU" if world == 1 else f"scene = {world} shards of {len(p)} points, model replicated, "
-                   "NCCL all-reduce of 18+1 doubles per iteration",
+                   "sharding": "1 GPU" if world == 1 else f"scene = {world} shards of ~{len(p)} points "
+                   f"({p_global_n} in total), model replicated, {comm_kind}",
                    "l2": "flushed between steps (256 MB write)", "model_splits": st["n_splits"]},
         "roofline": {"bound": "fp32", "kernel": "nn_filter_kernel", "achieved": achieved, "peak": peak,
                      "unit": "TFLOP/s", "frac": achieved / peak, "peak_source": peak_src,
                      "algorithmic_flops_per_eval": 8, "evals_per_launch": len(m) * len(p),
                      "avg_launch_ms": filt_ms_per_launch,
                      "traffic": traffic["dram_bytes_per_launch"] if traffic else None},
-        "cpu_baseline": {"value": cv, "unit": "evals/s", "cores": cores, "kind": "port",
-                         "sample": f"{cit} ICP iteration(s), {len(pc)} scene x {len(m)} model points, oracle x*x+sqrt form"},
+        "cpu_baseline": cpu,
         "e2e": {"value": evals / e2e_s, "unit": "evals/s", "ms_per_step": e2e_s * 1e3,
                 "h2d_bytes_per_step": (len(m) + len(p)) * 24, "d2h_bytes_per_step": len(p) * 24 + it2 * 8 + 64},
         "gpu_launches": launches, "clocks": clocks,
@@ -279,10 +305,13 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="horse", choices=list(WORKLOADS) + list(SYNTHETIC))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = every rank holds a full copy of the scene as its shard (per-GPU work fixed); "
+                         "strong = the one scene is cut into N contiguous blocks")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

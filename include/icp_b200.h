@@ -55,6 +55,10 @@ typedef struct icp_stats {
     int32_t kernels_launched;   /* kernels launched by the last icp_run / operator call */
     float   ms_filter;          /* CUDA-event time of the FP32 filter kernel, summed over the last run */
     float   ms_total;           /* CUDA-event time of the last icp_run (device loop only) */
+    float   ms_refine;          /* ICP_PROFILE=1 only: event time of nn_refine / nn_exact / the fused alignment */
+    float   ms_exact;           /*   kernel summed over the last run (the extra events cost ~1 us per iteration) */
+    float   ms_align;
+    float   reserved_;
 } icp_stats;
 
 /* ---- lifetime ------------------------------------------------------------------------------- */
@@ -108,6 +112,11 @@ int icp_run(icp_ctx* ctx, int max_iter, double threshold, int check_sizes, int* 
 /* Correspondence indices of the last closest pass (any of icp_closest / icp_run). */
 int icp_get_indices(icp_ctx* ctx, int32_t* idx_out);
 int icp_get_stats(icp_ctx* ctx, icp_stats* out);
+/* Diagnostic (ICP_PROFILE=1 in the environment at icp_create): microseconds, relative to kernel entry, at which
+ * block 0 of the last fused alignment kernel passed: 1 moments loop done, 2 block partials written, 3 grid
+ * barrier passed, 4 partials reduced (+ peer exchange), 5 Horn solve done, 6 transform loop done, 7 exit of
+ * the LAST block; slot 0 = microseconds between the end of the preceding nearest-neighbour kernel and entry. */
+int icp_get_trace(icp_ctx* ctx, double out_us[8]);
 
 /* ---- stateless one-shot forms (host pointers in, host results out) — back the reference-shaped
  * wrappers of src/GPU/gpu.hh:110-116; each creates and destroys a context on device 0.
@@ -127,6 +136,17 @@ int icp_err_compute_host(const double* Y_xyz, double* p_xyz, int64_t np, int in_
 int icp_subtract_col_host(const double* M_xyz, int64_t n, const double m[3], double* out_xyz);
 int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, double* d_caps, double* sp);
 
+/* ---- batched registration (new: BASELINE.json configs[4], many independent pairs) ----------------------
+ * Runs CPU::ICP::find_corresponding (src/cpu.cc:55-79) on n_pairs independent (model, scene) pairs on one
+ * device.  `lanes` (1..8) contexts work concurrently, each on its own stream, so that one pair's latency-bound
+ * alignment steps and PCIe copies hide behind another pair's nearest-neighbour kernel.  Outputs (all nullable):
+ * iters_out[k], err_out[k] (last printed error value), new_p_out[k] (np[k] x 3 doubles), srt_out[13 k ..] =
+ * s, R[9] row-major, t[3] of the last iteration.  Across GPUs: one process per GPU, pairs dealt round-robin by
+ * the launcher; nothing is exchanged. */
+int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
+                  const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
+                  int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out);
+
 /* ---- multi-GPU (new; the reference is single-GPU) ----------------------------------------------
  * One context per GPU / rank holds a contiguous block of the scene and a replica of the model.
  * The per-iteration exchange is an all-reduce(sum) of 18 doubles of moments and of 1 double of
@@ -137,6 +157,14 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
 int icp_comm_unique_id(const char* nccl_library_path, void* id128);
 int icp_comm_init(icp_ctx* ctx, const char* nccl_library_path, const void* id128, int rank, int world);
 int icp_comm_world(icp_ctx* ctx, int* rank, int* world);
+/* Peer-memory exchange (preferred over the NCCL all-reduce once attached): every rank exports the CUDA IPC
+ * handle (64 bytes) of a small mailbox in its HBM, the launcher all-gathers the handles, and every rank
+ * maps its peers' mailboxes.  From then on the alignment kernel itself posts its 18 + 1 partial sums into
+ * all peers' mailboxes over NVLink and adds what it received in rank order: no collective launch per
+ * iteration.  One process per GPU; icp_comm_init must have been called (the size check still uses NCCL).
+ * ICP_COMM=nccl in the environment keeps the NCCL path for comparison. */
+int icp_comm_peer_handle(icp_ctx* ctx, void* handle64);
+int icp_comm_peer_attach(icp_ctx* ctx, const void* handles /* world x 64 bytes, rank order */, int rank, int world);
 
 #ifdef __cplusplus
 }

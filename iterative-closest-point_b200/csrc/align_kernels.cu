@@ -10,7 +10,11 @@
 // Centring is algebraic (S = sum a b^T - n mu_a mu_b^T, ...), so the centred copies p', y' that the
 // reference materialises (src/cpu.cc:116-117) never exist.  Reduction is a fixed two-level tree
 // (block partials -> last block), so results are run-to-run deterministic.
+#include <cooperative_groups.h>
+
 #include "icp_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace icpb {
 
@@ -40,15 +44,65 @@ __device__ __forceinline__ void block_sum(double (&v)[N], double* smem /* N * wa
 __device__ void horn_solve(const double* __restrict__ geo, const double* __restrict__ mom, double* __restrict__ xf);
 
 // ------------------------------------------------------------------------------------------------
+// Peer-memory all-reduce(sum) of n <= PEER_SLOT doubles, executed by the FIRST WARP of one block.
+// See PeerComm in icp_common.cuh.  `stage` is shared memory, PEER_MAX_WORLD x PEER_SLOT doubles.
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__device__ void peer_allreduce(const PeerComm& pc, unsigned long long seq, const double* vals, int n, double* out,
+                               double* stage, int* ctl)
+{
+    const int lane = threadIdx.x;                    // caller: threadIdx.x < 32
+    const int par = (int)(seq & 1ull);
+    if (lane < pc.world) {
+        PeerMailbox* dst = pc.box[lane];             // post to rank `lane` (own mailbox included)
+        for (int i = 0; i < n; ++i) dst->data[par][pc.rank][i] = vals[i];
+        __threadfence_system();
+        st_release_sys(&dst->flag[par][pc.rank], seq);
+        // wait for rank `lane`'s post in my own mailbox
+        PeerMailbox* mine = pc.box[pc.rank];
+        const unsigned long long t0 = globaltimer_ns();
+        while (ld_acquire_sys(&mine->flag[par][lane]) != seq) {
+            if (globaltimer_ns() - t0 > 20000000000ull) { ctl[CTL_COMM_TIMEOUT] = 1; break; }   // 20 s: a peer died
+        }
+        for (int i = 0; i < n; ++i) stage[lane * PEER_SLOT + i] = __ldcv(&mine->data[par][lane][i]);
+    }
+    __syncwarp();
+    if (lane < n) {
+        double acc = 0.0;
+        for (int r = 0; r < pc.world; ++r) acc += stage[r * PEER_SLOT + lane];     // rank order: identical everywhere
+        out[lane] = acc;
+    }
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------
 // K2: moments.
 __global__ void __launch_bounds__(RED_THREADS)
 moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
                const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
                const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
-               double* __restrict__ mom, int* __restrict__ ctl, int honor_done, double* __restrict__ xf_fused)
+               double* __restrict__ mom, int* __restrict__ ctl, int honor_done, double* __restrict__ xf_fused,
+               PeerComm pc, unsigned long long seq)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     __shared__ double red[17 * (RED_THREADS / 32)];
+    __shared__ double mom_s[MOM_N];
+    __shared__ double stage[PEER_MAX_WORLD * PEER_SLOT];
     __shared__ int is_last;
     const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
     double acc[17];
@@ -85,11 +139,18 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
             for (int i = 0; i < 17; ++i) tot[i] += partials[(size_t)b * 17 + i];
         block_sum<17>(tot, red);
         if (threadIdx.x == 0) {
-            mom[0] = (double)np;
+            mom_s[0] = (double)np;
 #pragma unroll
-            for (int i = 0; i < 17; ++i) mom[1 + i] = tot[i];
+            for (int i = 0; i < 17; ++i) mom_s[1 + i] = tot[i];
             ctl[CTL_TICKET_MOM] = 0;
-            if (xf_fused) horn_solve(geo, mom, xf_fused);   // single-GPU: K3 rides on K2's last block
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            // multi-GPU: the 18 sums of all ranks meet here, inside the kernel (peer mailboxes over NVLink)
+            if (pc.world > 0) peer_allreduce(pc, seq, mom_s, MOM_N, mom_s, stage, ctl);
+            if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
+            __syncwarp();
+            if (threadIdx.x == 0 && xf_fused) horn_solve(geo, mom_s, xf_fused);   // K3 rides on K2's last block
         }
     }
 }
@@ -273,6 +334,50 @@ __global__ void solve_kernel(const double* __restrict__ geo, const double* __res
     if (threadIdx.x == 0) horn_solve(geo, mom, xf);
 }
 
+// The per-point body of K4, shared by transform_kernel and align_fused_kernel.  Warps stay converged over
+// the last (ragged) 32 points so that the warp holding point np-1 can refresh the FP32 shadow's padding
+// [np, np_pad) cooperatively (one thread doing it alone costs ~20 us on horse: 667 dependent stores).
+__device__ __forceinline__ void transform_points(const double* __restrict__ m64x, const double* __restrict__ m64y,
+                                                 const double* __restrict__ m64z, double* __restrict__ p64x,
+                                                 double* __restrict__ p64y, double* __restrict__ p64z,
+                                                 float* __restrict__ phx, float* __restrict__ phy,
+                                                 float* __restrict__ phz, const int32_t* __restrict__ idx, int np,
+                                                 int np_pad, const double (&sr)[9], double tx, double ty, double tz,
+                                                 double c0x, double c0y, double c0z, int in_place, int n_blocks,
+                                                 double& acc)
+{
+    const int np_round = (np + 31) & ~31;
+    for (int j0 = blockIdx.x * RED_THREADS + threadIdx.x; j0 < np_round; j0 += n_blocks * RED_THREADS) {
+        const bool act = j0 < np;
+        const int j = act ? j0 : np - 1;
+        const int k = idx[j];
+        const double x = p64x[j], y = p64y[j], z = p64z[j];
+        const double qx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
+        const double qy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
+        const double qz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
+        const double ex = __dsub_rn(m64x[k], qx), ey = __dsub_rn(m64y[k], qy), ez = __dsub_rn(m64z[k], qz);
+        if (act) acc += __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
+        if (in_place) {                                   // uniform
+            // every lane has READ its point before any lane of this warp writes (the inactive lanes of the
+            // last warp re-read point np-1, which lives in this same warp)
+            __syncwarp();
+            float fx = (float)(qx - c0x), fy = (float)(qy - c0y), fz = (float)(qz - c0z);
+            if (act) {
+                p64x[j] = qx; p64y[j] = qy; p64z[j] = qz;
+                phx[j] = fx; phy[j] = fy; phz[j] = fz;
+            }
+            const unsigned has_last = __ballot_sync(0xffffffffu, j0 == np - 1);
+            if (has_last) {                               // warp-uniform: refresh the padding = last real point
+                const int src = __ffs(has_last) - 1;
+                fx = __shfl_sync(0xffffffffu, fx, src);
+                fy = __shfl_sync(0xffffffffu, fy, src);
+                fz = __shfl_sync(0xffffffffu, fz, src);
+                for (int q = np + (int)(threadIdx.x & 31); q < np_pad; q += 32) { phx[q] = fx; phy[q] = fy; phz[q] = fz; }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K4: fused transform + residual.  Per point q = sR p + t (evaluated as the reference does:
 // sr = s*R element-wise, then (sr0 x + sr1 y + sr2 z) + t, no FMA contraction), e = |y - q|^2.
@@ -286,10 +391,13 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
                  double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
                  const int32_t* __restrict__ idx, int np, int np_pad, const double* __restrict__ xf, int in_place,
                  double* __restrict__ partials, double* __restrict__ err_sum, int* __restrict__ ctl, int honor_done,
-                 int finish, double n_global, double threshold, double* __restrict__ err_hist)
+                 int finish, double n_global, double threshold, double* __restrict__ err_hist, PeerComm pc,
+                 unsigned long long seq)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     __shared__ double red[RED_THREADS / 32];
+    __shared__ double tot_s[1];
+    __shared__ double stage[PEER_MAX_WORLD * PEER_SLOT];
     __shared__ int is_last;
     const double s = xf[0];
     double sr[9];
@@ -298,22 +406,8 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
     const double tx = xf[10], ty = xf[11], tz = xf[12];
     const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
     double acc[1] = {0.0};
-    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < np; j += gridDim.x * RED_THREADS) {
-        const int k = idx[j];
-        const double x = p64x[j], y = p64y[j], z = p64z[j];
-        const double qx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
-        const double qy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
-        const double qz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
-        const double ex = __dsub_rn(m64x[k], qx), ey = __dsub_rn(m64y[k], qy), ez = __dsub_rn(m64z[k], qz);
-        acc[0] += __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
-        if (in_place) {
-            p64x[j] = qx; p64y[j] = qy; p64z[j] = qz;
-            const float fx = (float)(qx - c0x), fy = (float)(qy - c0y), fz = (float)(qz - c0z);
-            phx[j] = fx; phy[j] = fy; phz[j] = fz;
-            if (j == np - 1)   // keep the padding of the FP32 shadow equal to the last real point
-                for (int q = np; q < np_pad; ++q) { phx[q] = fx; phy[q] = fy; phz[q] = fz; }
-        }
-    }
+    transform_points(m64x, m64y, m64z, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
+                     in_place, (int)gridDim.x, acc[0]);
     block_sum<1>(acc, red);
     if (threadIdx.x == 0) {
         partials[blockIdx.x] = acc[0];
@@ -327,15 +421,21 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         double tot[1] = {0.0};
         for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS) tot[0] += partials[b];
         block_sum<1>(tot, red);
-        if (threadIdx.x == 0) {
-            err_sum[0] = tot[0];
-            ctl[CTL_TICKET_ERR] = 0;
-            if (finish) {
-                const int it = ctl[CTL_ITERS];
-                const double err = (tot[0] + tot[0]) / n_global;
-                err_hist[it] = err;
-                ctl[CTL_ITERS] = it + 1;
-                if (err < threshold) ctl[CTL_DONE] = 1;
+        if (threadIdx.x == 0) tot_s[0] = tot[0];
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            if (pc.world > 0) peer_allreduce(pc, seq, tot_s, 1, tot_s, stage, ctl);
+            if (threadIdx.x == 0) {
+                const double total = tot_s[0];
+                err_sum[0] = total;
+                ctl[CTL_TICKET_ERR] = 0;
+                if (finish) {
+                    const int it = ctl[CTL_ITERS];
+                    const double err = (total + total) / n_global;
+                    err_hist[it] = err;
+                    ctl[CTL_ITERS] = it + 1;
+                    if (err < threshold) ctl[CTL_DONE] = 1;
+                }
             }
         }
     }
@@ -351,6 +451,151 @@ __global__ void finish_kernel(const double* __restrict__ err_sum, double n_globa
     err_hist[it] = err;
     ctl[CTL_ITERS] = it + 1;
     if (err < threshold) ctl[CTL_DONE] = 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 + K3 + K4 fused (cooperative launch, all blocks co-resident):
+//   phase M  17 moment sums of this block's points                      -> partials[block][17]
+//   grid barrier
+//   phase S  every block adds the partials in the same fixed order (bit-identical totals) and its
+//            thread 0 runs the Horn solve into shared memory: no second barrier, no broadcast.
+//            peers attached (pc.world > 0): block 0 alone reduces, exchanges the 18 sums with its peers through NVLink
+//            mailboxes, publishes the global sums, second grid barrier, then every block solves.
+//   phase T  q = sR p + t, residual; in_place writes new_p and its FP32 shadow  -> partials_err[block]
+//   last block (ticket): total residual (+ peer exchange), closes the iteration when `finish`.
+__global__ void __launch_bounds__(RED_THREADS, 2)
+align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
+                   const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
+                   double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
+                   const int32_t* __restrict__ idx, int np, int np_pad, double* __restrict__ partials,
+                   double* __restrict__ mom, double* __restrict__ xf, double* __restrict__ err_sum,
+                   int* __restrict__ ctl, int honor_done, int in_place, int finish, double n_global, double threshold,
+                   double* __restrict__ err_hist, PeerComm pc, unsigned long long seq,
+                   unsigned long long* __restrict__ trace)
+{
+    if (honor_done && ctl[CTL_DONE]) return;                 // uniform over the grid: nobody reaches a barrier
+    // diagnostic (ICP_PROFILE=1): block 0 stamps %globaltimer at its phase boundaries
+#define TRACE(slot) do { if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[slot] = globaltimer_ns(); } while (0)
+    TRACE(0);
+    cg::grid_group grid = cg::this_grid();
+    __shared__ double red[17 * (RED_THREADS / 32)];
+    __shared__ double mom_s[MOM_N];
+    __shared__ double xf_s[XF_N];
+    __shared__ double stage[PEER_MAX_WORLD * PEER_SLOT];
+    __shared__ int is_last;
+    const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
+    const int nb = (int)gridDim.x;
+    double* partials_err = partials + (size_t)nb * 17;
+
+    // ---- phase M ------------------------------------------------------------------------------
+    double acc[17];
+#pragma unroll
+    for (int i = 0; i < 17; ++i) acc[i] = 0.0;
+    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < np; j += nb * RED_THREADS) {
+        const int k = idx[j];
+        const double ax = p64x[j] - c0x, ay = p64y[j] - c0y, az = p64z[j] - c0z;
+        const double bx = m64x[k] - c0x, by = m64y[k] - c0y, bz = m64z[k] - c0z;
+        acc[0] += ax; acc[1] += ay; acc[2] += az;
+        acc[3] += bx; acc[4] += by; acc[5] += bz;
+        acc[6] += ax * bx; acc[7] += ax * by; acc[8] += ax * bz;
+        acc[9] += ay * bx; acc[10] += ay * by; acc[11] += ay * bz;
+        acc[12] += az * bx; acc[13] += az * by; acc[14] += az * bz;
+        acc[15] += ax * ax + ay * ay + az * az;
+        acc[16] += bx * bx + by * by + bz * bz;
+    }
+    TRACE(1);
+    block_sum<17>(acc, red);
+    if (threadIdx.x == 0)
+#pragma unroll
+        for (int i = 0; i < 17; ++i) partials[(size_t)blockIdx.x * 17 + i] = acc[i];
+    TRACE(2);
+    grid.sync();
+    TRACE(3);
+
+    // ---- phase S ------------------------------------------------------------------------------
+    if (pc.world == 0 || blockIdx.x == 0) {
+        double tot[17];
+#pragma unroll
+        for (int i = 0; i < 17; ++i) tot[i] = 0.0;
+        for (int b = threadIdx.x; b < nb; b += RED_THREADS)
+#pragma unroll
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)b * 17 + i]);
+        block_sum<17>(tot, red);
+        if (threadIdx.x == 0) {
+            mom_s[0] = (double)np;
+#pragma unroll
+            for (int i = 0; i < 17; ++i) mom_s[1 + i] = tot[i];
+        }
+        __syncthreads();
+    }
+    if (pc.world > 0) {
+        if (blockIdx.x == 0) {
+            if (threadIdx.x < 32) {
+                peer_allreduce(pc, seq, mom_s, MOM_N, mom_s, stage, ctl);
+                if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
+                __threadfence();
+            }
+        }
+        grid.sync();
+        if (blockIdx.x != 0 && threadIdx.x < MOM_N) mom_s[threadIdx.x] = __ldcg(&mom[threadIdx.x]);
+        __syncthreads();
+    }
+    TRACE(4);
+    if (threadIdx.x == 0) {
+        horn_solve(geo, mom_s, xf_s);
+        if (blockIdx.x == 0) {
+            for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];
+            if (pc.world == 0)
+                for (int i = 0; i < MOM_N; ++i) mom[i] = mom_s[i];
+        }
+    }
+    __syncthreads();
+    TRACE(5);
+
+    // ---- phase T ------------------------------------------------------------------------------
+    const double s = xf_s[0];
+    double sr[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(s, xf_s[1 + i]);
+    const double tx = xf_s[10], ty = xf_s[11], tz = xf_s[12];
+    double e[1] = {0.0};
+    transform_points(m64x, m64y, m64z, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
+                     in_place, nb, e[0]);
+    TRACE(6);
+    block_sum<1>(e, red);
+    if (threadIdx.x == 0) {
+        partials_err[blockIdx.x] = e[0];
+        __threadfence();
+        const int t = atomicAdd(&ctl[CTL_TICKET_ERR], 1);
+        is_last = (t == nb - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double tot[1] = {0.0};
+        for (int b = threadIdx.x; b < nb; b += RED_THREADS) tot[0] += __ldcg(&partials_err[b]);
+        block_sum<1>(tot, red);
+        if (threadIdx.x == 0) mom_s[0] = tot[0];
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            if (pc.world > 0) peer_allreduce(pc, seq + 1, mom_s, 1, mom_s, stage, ctl);
+            if (threadIdx.x == 0) {
+                const double total = mom_s[0];
+                err_sum[0] = total;
+                ctl[CTL_TICKET_ERR] = 0;
+                if (finish) {   // src/cpu.cc:67-77: the two residual sums are the same expression
+                    const int it = ctl[CTL_ITERS];
+                    const double err = (total + total) / n_global;
+                    err_hist[it] = err;
+                    ctl[CTL_ITERS] = it + 1;
+                    if (err < threshold) ctl[CTL_DONE] = 1;
+                }
+                if (trace) trace[9] = globaltimer_ns();      // the LAST block is done
+            }
+        }
+    }
+    TRACE(7);
+#undef TRACE
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -542,10 +787,12 @@ int reduce_blocks_for(int64_t n, int sm_count)
 }
 
 void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
-                    int honor_done, double* xf_fused, cudaStream_t st)
+                    int honor_done, double* xf_fused, cudaStream_t st, const PeerComm* peer, unsigned long long seq)
 {
+    PeerComm pc;
+    if (peer) pc = *peer;
     moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
-                                                     (int)s.np, partials, mom, ctl, honor_done, xf_fused);
+                                                     (int)s.np, partials, mom, ctl, honor_done, xf_fused, pc, seq);
 }
 
 void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st)
@@ -555,12 +802,40 @@ void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* c
 
 void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, int in_place, double* partials,
                       int n_blocks, double* err_sum, int* ctl, int honor_done, int finish, double n_global,
-                      double threshold, double* err_hist, cudaStream_t st)
+                      double threshold, double* err_hist, cudaStream_t st, const PeerComm* peer, unsigned long long seq)
 {
+    PeerComm pc;
+    if (peer) pc = *peer;
     transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
                                                        s.phy, s.phz, s.idx, (int)s.np, (int)s.np_pad, xf, in_place,
                                                        partials, err_sum, ctl, honor_done, finish, n_global,
-                                                       threshold, err_hist);
+                                                       threshold, err_hist, pc, seq);
+}
+
+int align_fused_max_blocks(int sm_count)
+{
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, align_fused_kernel, RED_THREADS, 0) != cudaSuccess || per_sm < 1)
+        per_sm = 1;
+    if (per_sm > 4) per_sm = 4;
+    return per_sm * sm_count;
+}
+
+int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, double* xf,
+                       double* err_sum, int* ctl, int honor_done, int in_place, int finish, double n_global,
+                       double threshold, double* err_hist, const PeerComm* peer, unsigned long long seq,
+                       unsigned long long* trace, cudaStream_t st)
+{
+    PeerComm pc;
+    if (peer) pc = *peer;
+    int np = (int)s.np, np_pad = (int)s.np_pad;
+    const double *a0 = m.m64x, *a1 = m.m64y, *a2 = m.m64z, *a3 = m.geo;
+    double *b0 = s.p64x, *b1 = s.p64y, *b2 = s.p64z;
+    float *f0 = s.phx, *f1 = s.phy, *f2 = s.phz;
+    const int32_t* ix = s.idx;
+    void* args[] = {&a0, &a1, &a2, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum,
+                    &ctl, &honor_done, &in_place, &finish, &n_global, &threshold, &err_hist, &pc, &seq, &trace};
+    return (int)cudaLaunchCooperativeKernel((const void*)align_fused_kernel, dim3(n_blocks), dim3(RED_THREADS), args, 0, st);
 }
 
 void launch_finish(const double* err_sum, double n_global, double threshold, double* err_hist, int* ctl,

@@ -7,10 +7,13 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <dlfcn.h>
 
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/icp_b200.h"
@@ -100,6 +103,14 @@ struct icp_ctx {
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
     int forced_splits = 0;
+    // fused alignment kernel (cooperative) and the peer-memory exchange it carries when world > 1
+    int align_blocks_max = 148;
+    PeerMailbox* d_mailbox = nullptr;
+    PeerComm peer;
+    bool peer_ready = false, force_nccl = false, align_fused = false;
+    unsigned long long seq = 0;            // exchanges issued so far (identical on every rank)
+    unsigned long long* d_trace = nullptr; // ICP_PROFILE=1: phase time stamps of the last fused alignment kernel
+    bool profile = false;                  // ICP_PROFILE=1: events between all kernels of icp_run (adds ~us per iteration)
 };
 
 namespace {
@@ -167,14 +178,55 @@ int allreduce(icp_ctx* c, double* buf, size_t n)
 }
 
 // One closest-matrix pass (K1) on the stream.
-void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1)
+void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1, cudaEvent_t e2 = nullptr,
+             cudaEvent_t e3 = nullptr)
 {
     if (e0) cudaEventRecord(e0, c->st);
     launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
     if (e1) cudaEventRecord(e1, c->st);
     launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
-    launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st);
+    if (e2) cudaEventRecord(e2, c->st);
+    launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st, c->profile ? c->d_trace : nullptr);
+    if (e3) cudaEventRecord(e3, c->st);
     c->stats.kernels_launched += 3;
+}
+
+// Alignment step (K2 -> K3 -> K4) of one iteration.  Two device-only forms, both carrying the multi-GPU
+// exchange INSIDE the kernels once peer mailboxes are attached:
+//   split (default)  moments_kernel (last block: reduce, exchange, Horn solve) + transform_kernel (last block:
+//                    reduce, exchange, close the iteration): 2 launches, no grid barrier
+//   fused            ICP_ALIGN=fused: one cooperative launch with a grid barrier (align_fused_kernel)
+// A communicator without mailboxes (or ICP_COMM=nccl) takes the NCCL path: separate kernels + ncclAllReduce.
+bool nccl_path(const icp_ctx* c) { return c->comm && (!c->peer_ready || c->force_nccl); }
+
+int fused_blocks(const icp_ctx* c)
+{
+    int64_t b = (c->s.np + RED_THREADS - 1) / RED_THREADS;
+    if (b > c->align_blocks_max) b = c->align_blocks_max;
+    return b < 1 ? 1 : (int)b;
+}
+
+// Enqueues one alignment step (not the NCCL path).  Consumes two exchange sequence numbers when peers are attached.
+// Returns the number of kernels launched (> 0) or a negative icp_status.
+int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_global, double threshold)
+{
+    const PeerComm* peers = (c->comm && c->peer_ready) ? &c->peer : nullptr;
+    int launched;
+    if (c->align_fused) {
+        const int e = launch_align_fused(c->m, c->s, c->d_partials, fused_blocks(c), c->d_mom, c->d_xf, c->d_err_sum,
+                                         c->d_ctl, honor_done, in_place, finish, n_global, threshold, c->d_err_hist, peers,
+                                         c->seq + 1, c->profile ? c->d_trace : nullptr, c->st);
+        if (e != 0) { g_err = std::string("align_fused launch: ") + cudaGetErrorString((cudaError_t)e); return ICP_ERR_CUDA; }
+        launched = 1;
+    } else {
+        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, honor_done, c->d_xf, c->st, peers,
+                       c->seq + 1);
+        launch_transform(c->m, c->s, c->d_xf, in_place, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, honor_done,
+                         finish, n_global, threshold, c->d_err_hist, c->st, peers, c->seq + 2);
+        launched = 2;
+    }
+    if (peers) c->seq += 2;
+    return launched;
 }
 
 int reset_ctl(icp_ctx* c)
@@ -232,10 +284,16 @@ int icp_create(icp_ctx** out, int device)
     int r;
     if ((r = dalloc(&c->d_mom, MOM_N)) || (r = dalloc(&c->d_xf, XF_N)) || (r = dalloc(&c->d_err_sum, 1)) ||
         (r = dalloc(&c->d_out6, 8)) || (r = dalloc(&c->d_ctl, CTL_N)) || (r = dalloc(&c->m.geo, 16)) ||
-        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 17))) {
+        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 18))) {
         delete c;
         return r;
     }
+    if ((r = dalloc(&c->d_trace, 16))) { delete c; return r; }
+    CK(cudaMemset(c->d_trace, 0, 16 * sizeof(unsigned long long)));
+    c->align_blocks_max = align_fused_max_blocks(c->sm_count);
+    if (const char* e = getenv("ICP_COMM")) c->force_nccl = !strcmp(e, "nccl");
+    if (const char* e = getenv("ICP_ALIGN")) c->align_fused = !strcmp(e, "fused");
+    if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
     if (const char* e = getenv("ICP_NN_SPLITS")) c->forced_splits = atoi(e);
     if ((r = set_identity_xf(c))) { delete c; return r; }
@@ -249,10 +307,14 @@ void icp_destroy(icp_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->st);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (int r = 0; r < c->peer.world; ++r)
+        if (c->peer_ready && r != c->peer.rank && c->peer.box[r]) cudaIpcCloseMemHandle(c->peer.box[r]);
+    dfree(c->d_mailbox); dfree(c->d_trace);
     dfree(c->m.m64x); dfree(c->m.m64y); dfree(c->m.m64z); dfree(c->m.mhat); dfree(c->m.geo);
     dfree(c->s.p64x); dfree(c->s.p64y); dfree(c->s.p64z); dfree(c->s.q64x); dfree(c->s.q64y); dfree(c->s.q64z);
     dfree(c->s.phx); dfree(c->s.phy); dfree(c->s.phz); dfree(c->s.perm); dfree(c->s.idx);
-    dfree(c->sc.best); dfree(c->sc.runner); dfree(c->sc.chunk); dfree(c->sc.amb_list);
+    dfree(c->sc.best); dfree(c->sc.runner); dfree(c->sc.chunk); dfree(c->sc.amb_list); dfree(c->sc.amb_thr);
+    dfree(c->sc.seg_v); dfree(c->sc.seg_k); dfree(c->sc.batch_ticket);
     dfree(c->d_stage); dfree(c->d_partials); dfree(c->d_mom); dfree(c->d_xf); dfree(c->d_err_sum); dfree(c->d_out6);
     dfree(c->d_err_hist); dfree(c->d_ctl); dfree(c->d_keys); dfree(c->d_keys_alt); dfree(c->d_vals);
     dfree(c->d_idx_out);
@@ -304,8 +366,16 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
             (r = dalloc(&c->s.q64y, (size_t)np)) || (r = dalloc(&c->s.q64z, (size_t)np)) ||
             (r = dalloc(&c->s.phx, (size_t)np_pad)) || (r = dalloc(&c->s.phy, (size_t)np_pad)) ||
             (r = dalloc(&c->s.phz, (size_t)np_pad)) || (r = dalloc(&c->s.perm, (size_t)np)) ||
-            (r = dalloc(&c->s.idx, (size_t)np)) || (r = dalloc(&c->sc.amb_list, (size_t)np)))
+            (r = dalloc(&c->s.idx, (size_t)np)) || (r = dalloc(&c->sc.amb_list, (size_t)np)) ||
+            (r = dalloc(&c->sc.amb_thr, (size_t)np)))
             return r;
+        // nn_exact scratch: per (model segment, queued point) minima + one ticket per batch of queued points
+        c->sc.seg_cap = (size_t)np + 65536;
+        const size_t n_tickets = (size_t)np / nn_exact_batch_points() + 2;
+        if ((r = dalloc(&c->sc.seg_v, c->sc.seg_cap)) || (r = dalloc(&c->sc.seg_k, c->sc.seg_cap)) ||
+            (r = dalloc(&c->sc.batch_ticket, n_tickets)))
+            return r;
+        CK(cudaMemsetAsync(c->sc.batch_ticket, 0, n_tickets * sizeof(int), c->st));
     }
     // Morton sort of the scene (once per scene; a similarity transform keeps tiles compact)
     if (c->sort_cap < (size_t)np) {
@@ -453,20 +523,23 @@ int icp_find_alignment(icp_ctx* c, double* s, double R[9], double t[3], double* 
     int r;
     if ((r = need_idx(c, "icp_find_alignment"))) return r;
     CK(cudaSetDevice(c->device));
-    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, c->comm ? nullptr : c->d_xf, c->st);
-    if (c->comm) {
+    int launched = 3;
+    if (!nccl_path(c)) {
+        if ((launched = align_step(c, 0, 0, 0, 1.0, 0.0)) < 0) return launched;
+    } else {
+        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, nullptr, c->st);
         if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
         launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 0, c->st);
+        launch_transform(c->m, c->s, c->d_xf, 0, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 0, 0, 1.0, 0.0,
+                         nullptr, c->st);
+        if ((r = allreduce(c, c->d_err_sum, 1))) return r;
     }
-    launch_transform(c->m, c->s, c->d_xf, 0, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 0, 0, 1.0, 0.0,
-                     nullptr, c->st);
-    if ((r = allreduce(c, c->d_err_sum, 1))) return r;
     CK(cudaGetLastError());
     double e;
     CK(cudaMemcpyAsync(&e, c->d_err_sum, sizeof(e), cudaMemcpyDeviceToHost, c->st));
     if ((r = icp_get_transform(c, s, R, t))) return r;
     if (err_align) *err_align = e;
-    c->stats.kernels_launched = 3;
+    c->stats.kernels_launched = launched;
     return ICP_OK;
 }
 
@@ -510,7 +583,8 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
         if ((r = dalloc(&c->d_err_hist, (size_t)max_iter))) return r;
         c->err_hist_cap = max_iter;
     }
-    while ((int)c->ev_filter.size() < 2 * max_iter) {
+    const int EV = c->profile ? 5 : 2;     // events per iteration
+    while ((int)c->ev_filter.size() < EV * max_iter) {
         cudaEvent_t e;
         CK(cudaEventCreate(&e));
         c->ev_filter.push_back(e);
@@ -519,28 +593,30 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->stats.kernels_launched = 0;
     CK(cudaEventRecord(c->ev0, c->st));
     for (int it = 0; it < max_iter; ++it) {
-        nn_pass(c, 1, c->ev_filter[2 * it], c->ev_filter[2 * it + 1]);
-        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, c->comm ? nullptr : c->d_xf,
-                       c->st);
-        if (c->comm) {
-            if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
-            launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
-            c->stats.kernels_launched += 1;
+        cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
+        nn_pass(c, 1, ev[0], ev[1], c->profile ? ev[2] : nullptr, c->profile ? ev[3] : nullptr);
+        if (!nccl_path(c)) {
+            int launched = align_step(c, 1, 1, 1, np_glob, threshold);
+            if (launched < 0) return launched;
+            if (c->profile) cudaEventRecord(ev[4], c->st);
+            c->stats.kernels_launched += launched;
+            continue;
         }
-        launch_transform(c->m, c->s, c->d_xf, 1, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 1,
-                         c->comm ? 0 : 1, np_glob, threshold, c->d_err_hist, c->st);
-        c->stats.kernels_launched += 2;
-        if (c->comm) {
-            if ((r = allreduce(c, c->d_err_sum, 1))) return r;
-            launch_finish(c->d_err_sum, np_glob, threshold, c->d_err_hist, c->d_ctl, c->st);
-            c->stats.kernels_launched += 1;
-        }
+        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, nullptr, c->st);
+        if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+        launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
+        launch_transform(c->m, c->s, c->d_xf, 1, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 1, 0, np_glob,
+                         threshold, c->d_err_hist, c->st);
+        if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+        launch_finish(c->d_err_sum, np_glob, threshold, c->d_err_hist, c->d_ctl, c->st);
+        c->stats.kernels_launched += 4;
     }
     CK(cudaEventRecord(c->ev1, c->st));
     CK(cudaGetLastError());
     int ctl[CTL_N];
     CK(cudaMemcpyAsync(ctl, c->d_ctl, sizeof(ctl), cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
+    if (ctl[CTL_COMM_TIMEOUT]) { g_err = "peer exchange timed out (a rank did not arrive)"; return ICP_ERR_COMM; }
     const int iters = ctl[CTL_ITERS];
     if (iters_done) *iters_done = iters;
     if (err_hist && iters > 0)
@@ -551,13 +627,35 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->stats.rerank_full += ctl[CTL_AMB_TOTAL];
     c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
     cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
-    float f = 0.f;
+    float f = 0.f, f_ref = 0.f, f_ex = 0.f, f_al = 0.f;
     for (int it = 0; it < iters; ++it) {
+        cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
         float ms = 0.f;
-        cudaEventElapsedTime(&ms, c->ev_filter[2 * it], c->ev_filter[2 * it + 1]);
+        cudaEventElapsedTime(&ms, ev[0], ev[1]);
         f += ms;
+        if (c->profile && !nccl_path(c)) {
+            cudaEventElapsedTime(&ms, ev[1], ev[2]); f_ref += ms;
+            cudaEventElapsedTime(&ms, ev[2], ev[3]); f_ex += ms;
+            cudaEventElapsedTime(&ms, ev[3], ev[4]); f_al += ms;
+        }
     }
     c->stats.ms_filter = f;
+    c->stats.ms_refine = f_ref;
+    c->stats.ms_exact = f_ex;
+    c->stats.ms_align = f_al;
+    return ICP_OK;
+}
+
+int icp_get_trace(icp_ctx* c, double out_us[8])
+{
+    if (!c || !out_us) return ICP_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    unsigned long long t[16];
+    CK(cudaMemcpyAsync(t, c->d_trace, sizeof(t), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    for (int i = 0; i < 8; ++i) out_us[i] = t[i] >= t[0] ? (double)(t[i] - t[0]) * 1e-3 : 0.0;
+    out_us[0] = t[0] >= t[8] ? (double)(t[0] - t[8]) * 1e-3 : -1.0;     // gap: end of K1 -> entry of block 0
+    if (t[9] >= t[0]) out_us[7] = (double)(t[9] - t[0]) * 1e-3;         // exit of the LAST block instead of block 0
     return ICP_OK;
 }
 
@@ -678,6 +776,52 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
     return ICP_OK;
 }
 
+// ---- batched registration (BASELINE config 5: many independent cloud pairs) ----------------------
+// Pairs are independent, so there is nothing to exchange: `lanes` host threads each own a context (own
+// stream) on `device` and pull pairs from a shared counter.  While one lane is in the latency-bound
+// tail of an iteration (refine / exact / alignment) or copying over PCIe, the other lanes' filter
+// kernels keep the SMs busy.  Across GPUs the launcher deals pairs round-robin, one process per GPU.
+int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
+                  const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
+                  int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out)
+{
+    if (n_pairs < 0 || (n_pairs > 0 && (!m_xyz || !nm || !p_xyz || !np))) { g_err = "icp_batch_run: bad arguments"; return ICP_ERR_INVALID; }
+    if (lanes < 1) lanes = 1;
+    if (lanes > 8) lanes = 8;
+    if ((int64_t)lanes > n_pairs) lanes = n_pairs > 0 ? (int)n_pairs : 1;
+    std::atomic<int64_t> next{0};
+    std::atomic<int> status{ICP_OK};
+    std::mutex mu;
+    std::string first_err;
+    auto worker = [&]() {
+        icp_ctx* c = nullptr;
+        int r = icp_create(&c, device);
+        std::vector<double> hist((size_t)(max_iter > 0 ? max_iter : 1));
+        while (!r && status.load() == ICP_OK) {
+            const int64_t k = next.fetch_add(1);
+            if (k >= n_pairs) break;
+            int it = 0;
+            if ((r = icp_set_model(c, m_xyz[k], nm[k])) || (r = icp_set_scene(c, p_xyz[k], np[k])) ||
+                (r = icp_run(c, max_iter, threshold, check_sizes, &it, hist.data())))
+                break;
+            if (iters_out) iters_out[k] = it;
+            if (err_out) err_out[k] = it > 0 ? hist[(size_t)it - 1] : 0.0;
+            if (new_p_out && new_p_out[k] && (r = icp_get_scene(c, new_p_out[k]))) break;
+            if (srt_out && (r = icp_get_transform(c, srt_out + 13 * k, srt_out + 13 * k + 1, srt_out + 13 * k + 10))) break;
+        }
+        if (r) {
+            std::lock_guard<std::mutex> lk(mu);
+            if (status.load() == ICP_OK) { status.store(r); first_err = g_err; }
+        }
+        if (c) icp_destroy(c);
+    };
+    std::vector<std::thread> th;
+    for (int i = 0; i < lanes; ++i) th.emplace_back(worker);
+    for (auto& t : th) t.join();
+    if (status.load() != ICP_OK) g_err = first_err;
+    return status.load();
+}
+
 // ---- multi-GPU ----------------------------------------------------------------------------------
 
 int icp_comm_unique_id(const char* nccl_library_path, void* id128)
@@ -707,6 +851,45 @@ int icp_comm_init(icp_ctx* c, const char* nccl_library_path, const void* id128, 
     }
     c->rank = rank;
     c->world = world;
+    return ICP_OK;
+}
+
+int icp_comm_peer_handle(icp_ctx* c, void* handle64)
+{
+    if (!c || !handle64) { g_err = "icp_comm_peer_handle: bad arguments"; return ICP_ERR_INVALID; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    CK(cudaSetDevice(c->device));
+    if (!c->d_mailbox) {
+        CK(cudaMalloc((void**)&c->d_mailbox, sizeof(PeerMailbox)));
+        CK(cudaMemset(c->d_mailbox, 0, sizeof(PeerMailbox)));
+        CK(cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, c->d_mailbox));
+    memcpy(handle64, &h, 64);
+    return ICP_OK;
+}
+
+int icp_comm_peer_attach(icp_ctx* c, const void* handles, int rank, int world)
+{
+    if (!c || !handles || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !c->d_mailbox) {
+        g_err = "icp_comm_peer_attach: bad arguments (export the local handle first; world <= 16)";
+        return ICP_ERR_INVALID;
+    }
+    CK(cudaSetDevice(c->device));
+    for (int r = 0; r < PEER_MAX_WORLD; ++r) c->peer.box[r] = nullptr;
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) { c->peer.box[r] = c->d_mailbox; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)handles + (size_t)r * 64, 64);
+        void* p = nullptr;
+        CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        c->peer.box[r] = (PeerMailbox*)p;
+    }
+    c->peer.rank = rank;
+    c->peer.world = world;
+    c->peer_ready = true;
+    c->seq = 0;
     return ICP_OK;
 }
 

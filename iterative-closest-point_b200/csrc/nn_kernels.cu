@@ -242,29 +242,52 @@ __device__ __forceinline__ void group_argmin(double& v, int& k, unsigned mask = 
     }
 }
 
+// The filter's FP32 surrogate d' = |m_loc|^2 - 2 p_loc.m_loc, re-evaluated with the SAME operation
+// sequence as nn_filter_kernel (fsub, mul+fma+fma for W, three chained FMAs; FFMA2 is an IEEE FMA per
+// lane), so the value is bit-identical to what the filter minimised.  (cx,cy,cz) = the CTA origin of the
+// scene point's tile, (ax,ay,az) = -2 p_loc.
+__device__ __forceinline__ float surrogate32(const float4 mh, float cx, float cy, float cz, float ax, float ay, float az)
+{
+    const float x = __fsub_rn(mh.x, cx), y = __fsub_rn(mh.y, cy), z = __fsub_rn(mh.z, cz);
+    const float w = __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x)));
+    return __fmaf_rn(ax, x, __fmaf_rn(ay, y, __fmaf_rn(az, z, w)));
+}
+
 constexpr int REFINE_THREADS = 256;
 constexpr int RF = 8;    // lanes cooperating on one scene point
 
+// nn_refine: merges the model splits, derives the bound tau and the FP32 acceptance threshold
+// thr = best + tau (rounded up).  Every model point that can be the reference's argmin has d' <= thr.
+//  - runner > thr ("clear"): all such points lie in the best chunk.  Its 64 points are re-scored with the
+//    FP32 surrogate; only those with d' <= thr (typically one) are evaluated in FP64 with the
+//    reference's own expression, first minimum wins.
+//  - otherwise the point is queued with its threshold for nn_exact (FP32 rescan of the whole model).
 __global__ void __launch_bounds__(REFINE_THREADS)
 nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
-                 int nm, const double* __restrict__ geo, const double* __restrict__ p64x,
-                 const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
-                 const float* __restrict__ phy, const float* __restrict__ phz, int np, int np_pad, int n_splits,
-                 const float* __restrict__ part_best, const float* __restrict__ part_runner,
+                 const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
+                 const double* __restrict__ p64x, const double* __restrict__ p64y, const double* __restrict__ p64z,
+                 const float* __restrict__ phx, const float* __restrict__ phy, const float* __restrict__ phz, int np,
+                 int np_pad, int n_splits, const float* __restrict__ part_best, const float* __restrict__ part_runner,
                  const uint32_t* __restrict__ part_chunk, int32_t* __restrict__ idx, int32_t* __restrict__ amb_list,
-                 int* __restrict__ ctl, int honor_done)
+                 float* __restrict__ amb_thr, int* __restrict__ ctl, int honor_done)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     const int lane = threadIdx.x & 31, sub = lane & (RF - 1), grp = lane / RF;
     const int warp = (blockIdx.x * REFINE_THREADS + threadIdx.x) >> 5;
     const int n_warps = (gridDim.x * REFINE_THREADS) >> 5;
     constexpr int PPW = 32 / RF;                       // scene points per warp
-    const double Rm = geo[3];
+    const float Rm = __double2float_ru(geo[3]);
     const float INF = __int_as_float(0x7f800000);
+    const unsigned gmask = ((1u << RF) - 1u) << (grp * RF);
 
     for (int jb = warp * PPW; jb < np; jb += n_warps * PPW) {
         const bool valid = jb + grp < np;
         const int j = valid ? jb + grp : np - 1;
+        // everything the point needs, requested up front so the latencies overlap
+        const int cj = (j / NN_TILE) * NN_TILE + NN_TILE / 2;
+        const float hx = phx[j], hy = phy[j], hz = phz[j];
+        const float cx = phx[cj], cy = phy[cj], cz = phz[cj];
+        const double px = p64x[j], py = p64y[j], pz = p64z[j];
         // ---- merge the model splits (RF lanes stride over the splits) ------------------------------
         float b = INF, rn = INF;
         uint32_t ch = 0;
@@ -286,94 +309,182 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         for (int o = RF / 2; o > 0; o >>= 1) runner = fminf(runner, __shfl_xor_sync(0xffffffffu, runner, o));
         const uint32_t chunk = __shfl_sync(0xffffffffu, ch, grp * RF + src);
 
-        // ---- rigorous FP32 error bound ------------------------------------------------------------
-        const int cj = (j / NN_TILE) * NN_TILE + NN_TILE / 2;
-        const float hx = phx[j], hy = phy[j], hz = phz[j];
-        const float lx = __fsub_rn(hx, phx[cj]), ly = __fsub_rn(hy, phy[cj]), lz = __fsub_rn(hz, phz[cj]);
-        const double P2 = (double)lx * lx + (double)ly * ly + (double)lz * lz;
-        const double P = sqrt(P2);
-        const double H = sqrt((double)hx * hx + (double)hy * hy + (double)hz * hz);
-        const double u = 5.9604644775390625e-8;                       // 2^-24
-        const double D0 = fmax((double)best + P2, 0.0);
-        double r = sqrt(D0);
-        double M = P + r;
-        double E = 6.5 * u * (M * M + 2.0 * P * M);
-        r = sqrt(D0 + E) * (1.0 + 1e-6);
-        M = P + r;
-        E = 6.5 * u * (M * M + 2.0 * P * M);
-        const double eta = 1.01 * u * (H + Rm + 2.0 * P + r);
-        const double tau = 2.0 * E + 4.0 * eta * r + 4.0 * eta * eta + 9.1e-13 * r * r;
-        const bool clear = (double)runner > (double)best + tau;       // false for NaN/inf oddities too
+        // ---- rigorous error bound, evaluated in FP32 with every operation rounded UP (all terms are
+        //      non-negative, so the result is >= the real-valued formula of DESIGN.md §K1) --------------
+        const float lx = __fsub_rn(hx, cx), ly = __fsub_rn(hy, cy), lz = __fsub_rn(hz, cz);   // p_loc, as in the filter
+        const float P2 = __fmaf_ru(lz, lz, __fmaf_ru(ly, ly, __fmul_ru(lx, lx)));
+        const float P = __fsqrt_ru(P2);
+        const float H = __fsqrt_ru(__fmaf_ru(hz, hz, __fmaf_ru(hy, hy, __fmul_ru(hx, hx))));
+        const float U65 = 3.8743021e-7f;                              // > 6.5 * 2^-24
+        const float U101 = 6.0201e-8f;                                 // > 1.01 * 2^-24
+        const float D0 = fmaxf(__fadd_ru(best, P2), 0.0f);
+        float r = __fsqrt_ru(D0);
+        float M = __fadd_ru(P, r);
+        float E = __fmul_ru(U65, __fmaf_ru(M, M, __fmul_ru(__fmul_ru(2.0f, P), M)));
+        r = __fmul_ru(__fsqrt_ru(__fadd_ru(D0, E)), 1.000001f);
+        M = __fadd_ru(P, r);
+        E = __fmul_ru(U65, __fmaf_ru(M, M, __fmul_ru(__fmul_ru(2.0f, P), M)));
+        const float eta = __fmul_ru(U101, __fadd_ru(__fadd_ru(H, Rm), __fadd_ru(__fmul_ru(2.0f, P), r)));
+        float tau = __fmul_ru(2.0f, E);
+        tau = __fmaf_ru(__fmul_ru(4.0f, eta), r, tau);
+        tau = __fmaf_ru(__fmul_ru(4.0f, eta), eta, tau);
+        tau = __fmaf_ru(__fmul_ru(9.1e-13f, r), r, tau);
+        tau = fmaxf(tau, 1.0e-37f);                                   // never let the margin underflow to zero
+        const float thr = __fadd_ru(best, tau);                       // NaN / +inf: everything is a candidate
+        const bool clear = runner > thr && thr < INF;                 // false for NaN/inf oddities too
 
         if (clear) {
-            // ---- FP64 re-rank of the best chunk with the reference's expression -------------------
-            const double px = p64x[j], py = p64y[j], pz = p64z[j];
+            // ---- best chunk: FP32 surrogate against thr, FP64 only for the survivors ---------------
+            const float ax = -2.0f * lx, ay = -2.0f * ly, az = -2.0f * lz;
             const int k0 = (int)chunk * NN_G;
-            double s2[NN_G / RF];
+            unsigned cand = 0u;
 #pragma unroll
-            for (int i = 0; i < NN_G / RF; ++i) {
-                const int kk = min(k0 + i * RF + sub, nm - 1);
-                s2[i] = dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]);
+            for (int i = 0; i < NN_G / RF; ++i) {    // mhat is padded to a multiple of NN_TM >= k0 + NN_G
+                const float d = surrogate32(mhat[k0 + i * RF + sub], cx, cy, cz, ax, ay, az);
+                if (!(d > thr) && k0 + i * RF + sub < nm) cand |= 1u << i;
             }
             Best64 bt;
             bt.init();
-#pragma unroll
-            for (int i = 0; i < NN_G / RF; ++i) {
+            while (cand) {                           // ascending i = ascending model index
+                const int i = __ffs(cand) - 1;
+                cand &= cand - 1u;
                 const int kk = k0 + i * RF + sub;
-                if (kk < nm) bt.feed(s2[i], kk);
+                bt.feed(dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]), kk);
             }
             double v = bt.v;
             int k = bt.k;
-            group_argmin<RF>(v, k, ((1u << RF) - 1u) << (grp * RF));   // `clear` is uniform per group, not per warp
+            group_argmin<RF>(v, k, gmask);             // `clear` is uniform per group, not per warp
             if (sub == 0 && valid) idx[j] = k;
         } else if (sub == 0 && valid) {
             const int pos = atomicAdd(&ctl[CTL_AMB_COUNT], 1);
             amb_list[pos] = j;
+            amb_thr[pos] = thr;
         }
     }
 }
 
-// Full FP64 scan for the scene points the filter could not decide.  One CTA per queued point; the
-// last CTA to finish folds the pass's counters into the totals.
+// nn_exact: the scene points the chunk test could not decide.  FP32 rescan of the WHOLE model with the
+// filter's surrogate; every model point with d' <= thr (a superset of the reference's possible argmins)
+// is evaluated in FP64 with the reference's expression; first minimum wins.
+// Work item = (batch of EX_P queued points) x (model segment); a model point is loaded once per batch.
+// Segment results are merged by the last CTA to finish a batch (ticket per batch).
 constexpr int EXACT_THREADS = 256;
+constexpr int EX_P = 4;          // queued points per batch
+constexpr int EX_U = 4;          // model points in flight per thread
+constexpr int EX_MIN_SEG = 4096; // model points per segment at least
 
 __global__ void __launch_bounds__(EXACT_THREADS)
 nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
-                int nm, const double* __restrict__ p64x, const double* __restrict__ p64y,
-                const double* __restrict__ p64z, const int32_t* __restrict__ amb_list, int32_t* __restrict__ idx,
-                int* __restrict__ ctl, int np, int honor_done)
+                const float4* __restrict__ mhat, int nm, int nm_pad, const double* __restrict__ p64x,
+                const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
+                const float* __restrict__ phy, const float* __restrict__ phz, const int32_t* __restrict__ amb_list,
+                const float* __restrict__ amb_thr, int32_t* __restrict__ idx, double* __restrict__ seg_v,
+                int32_t* __restrict__ seg_k, int seg_cap, int* __restrict__ batch_ticket, int* __restrict__ ctl, int np,
+                int honor_done, unsigned long long* __restrict__ trace)
 {
     if (honor_done && ctl[CTL_DONE]) return;
-    __shared__ double sv[EXACT_THREADS / 32];
-    __shared__ int sk[EXACT_THREADS / 32];
+    __shared__ double sp[EX_P][3];
+    __shared__ double sv[EX_P][EXACT_THREADS / 32];
+    __shared__ int sk[EX_P][EXACT_THREADS / 32];
+    __shared__ int s_last;
     const int count = ctl[CTL_AMB_COUNT];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int a = blockIdx.x; a < count; a += gridDim.x) {
-        const int j = amb_list[a];
-        const double px = p64x[j], py = p64y[j], pz = p64z[j];
-        Best64 bt;
-        bt.init();
-        int kk = threadIdx.x;
-        for (; kk + 3 * EXACT_THREADS < nm; kk += 4 * EXACT_THREADS) {    // 4 independent evaluations in flight
-            const double s0 = dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]);
-            const double s1 = dist2_64(px, py, pz, m64x[kk + EXACT_THREADS], m64y[kk + EXACT_THREADS], m64z[kk + EXACT_THREADS]);
-            const double s2 = dist2_64(px, py, pz, m64x[kk + 2 * EXACT_THREADS], m64y[kk + 2 * EXACT_THREADS], m64z[kk + 2 * EXACT_THREADS]);
-            const double s3 = dist2_64(px, py, pz, m64x[kk + 3 * EXACT_THREADS], m64y[kk + 3 * EXACT_THREADS], m64z[kk + 3 * EXACT_THREADS]);
-            bt.feed(s0, kk); bt.feed(s1, kk + EXACT_THREADS); bt.feed(s2, kk + 2 * EXACT_THREADS); bt.feed(s3, kk + 3 * EXACT_THREADS);
+    const int n_batches = (count + EX_P - 1) / EX_P;
+    // segments: enough items to fill the grid twice, bounded by the segment floor and the scratch
+    int n_seg = 1;
+    if (n_batches > 0) {
+        n_seg = (2 * (int)gridDim.x + n_batches - 1) / n_batches;
+        n_seg = min(n_seg, max(1, nm / EX_MIN_SEG));
+        n_seg = min(n_seg, max(1, seg_cap / (n_batches * EX_P)));
+    }
+    const int seg_len = ((nm + n_seg - 1) / n_seg + EXACT_THREADS * EX_U - 1) / (EXACT_THREADS * EX_U) * (EXACT_THREADS * EX_U);
+    const int items = n_batches * n_seg;
+    const double DINF = __longlong_as_double(0x7ff0000000000000LL);
+
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int batch = item / n_seg, seg = item - batch * n_seg;
+        const int a0 = batch * EX_P;
+        int jj[EX_P];
+        float cx[EX_P], cy[EX_P], cz[EX_P], ax[EX_P], ay[EX_P], az[EX_P], thr[EX_P];
+#pragma unroll
+        for (int p = 0; p < EX_P; ++p) {
+            const int a = min(a0 + p, count - 1);          // ragged last batch: duplicates, results dropped
+            const int j = amb_list[a];
+            jj[p] = j;
+            thr[p] = amb_thr[a];
+            const int cj = (j / NN_TILE) * NN_TILE + NN_TILE / 2;
+            cx[p] = phx[cj]; cy[p] = phy[cj]; cz[p] = phz[cj];
+            ax[p] = -2.0f * __fsub_rn(phx[j], cx[p]);
+            ay[p] = -2.0f * __fsub_rn(phy[j], cy[p]);
+            az[p] = -2.0f * __fsub_rn(phz[j], cz[p]);
         }
-        for (; kk < nm; kk += EXACT_THREADS) bt.feed(dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]), kk);
-        double v = bt.v;
-        int k = bt.k;
-        group_argmin<32>(v, k);
-        if (lane == 0) { sv[w] = v; sk[w] = k; }
+        __syncthreads();                                    // previous item's readers of sp/sv/sk are done
+        if (threadIdx.x < EX_P) {
+            const int j = amb_list[min(a0 + (int)threadIdx.x, count - 1)];
+            sp[threadIdx.x][0] = p64x[j];
+            sp[threadIdx.x][1] = p64y[j];
+            sp[threadIdx.x][2] = p64z[j];
+        }
+        __syncthreads();
+        Best64 bt[EX_P];
+#pragma unroll
+        for (int p = 0; p < EX_P; ++p) bt[p].init();
+        const int k_begin = seg * seg_len, k_end = min(k_begin + seg_len, nm);
+        for (int kb = k_begin + (int)threadIdx.x; kb < k_end; kb += EXACT_THREADS * EX_U) {
+            float4 mh[EX_U];
+#pragma unroll
+            for (int u = 0; u < EX_U; ++u) mh[u] = mhat[min(kb + u * EXACT_THREADS, nm_pad - 1)];
+#pragma unroll
+            for (int u = 0; u < EX_U; ++u) {
+                const int kk = kb + u * EXACT_THREADS;
+#pragma unroll
+                for (int p = 0; p < EX_P; ++p) {
+                    const float d = surrogate32(mh[u], cx[p], cy[p], cz[p], ax[p], ay[p], az[p]);
+                    if (!(d > thr[p]) && kk < k_end)
+                        bt[p].feed(dist2_64(sp[p][0], sp[p][1], sp[p][2], m64x[kk], m64y[kk], m64z[kk]), kk);
+                }
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < EX_P; ++p) {
+            double v = bt[p].v;
+            int k = bt[p].k;
+            group_argmin<32>(v, k);
+            if (lane == 0) { sv[p][w] = v; sk[p][w] = k; }
+        }
         __syncthreads();
         if (w == 0) {
-            v = lane < EXACT_THREADS / 32 ? sv[lane] : __longlong_as_double(0x7ff0000000000000LL);
-            k = lane < EXACT_THREADS / 32 ? sk[lane] : 0x7fffffff;
-            group_argmin<32>(v, k);
-            if (lane == 0) idx[j] = k;
+#pragma unroll
+            for (int p = 0; p < EX_P; ++p) {
+                double v = lane < EXACT_THREADS / 32 ? sv[p][lane] : DINF;
+                int k = lane < EXACT_THREADS / 32 ? sk[p][lane] : 0x7fffffff;
+                group_argmin<32>(v, k);
+                if (lane == 0 && a0 + p < count) {
+                    if (n_seg == 1) idx[jj[p]] = k;
+                    else { seg_v[(size_t)seg * n_batches * EX_P + a0 + p] = v; seg_k[(size_t)seg * n_batches * EX_P + a0 + p] = k; }
+                }
+            }
         }
-        __syncthreads();
+        if (n_seg > 1) {
+            if (threadIdx.x == 0) {
+                __threadfence();
+                const int t = atomicAdd(&batch_ticket[batch], 1);
+                s_last = (t == n_seg - 1);
+                if (s_last) batch_ticket[batch] = 0;
+            }
+            __syncthreads();
+            if (s_last && threadIdx.x < EX_P && a0 + (int)threadIdx.x < count) {
+                __threadfence();
+                double v = DINF;
+                int k = 0x7fffffff;
+                for (int s = 0; s < n_seg; ++s) {
+                    const double ov = seg_v[(size_t)s * n_batches * EX_P + a0 + threadIdx.x];
+                    const int ok = seg_k[(size_t)s * n_batches * EX_P + a0 + threadIdx.x];
+                    if (ov < v || (ov == v && ok < k)) { v = ov; k = ok; }
+                }
+                idx[amb_list[a0 + threadIdx.x]] = k;
+            }
+        }
     }
     if (threadIdx.x == 0) {
         __threadfence();
@@ -382,6 +493,7 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
             ctl[CTL_CHUNK_TOTAL] += np - count;
             ctl[CTL_AMB_COUNT] = 0;
             ctl[CTL_TICKET_NN] = 0;
+            if (trace) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(trace[8]));   // diagnostic: last block of K1 done
         }
     }
 }
@@ -411,20 +523,22 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
     int grid = (int)((warps * 32 + REFINE_THREADS - 1) / REFINE_THREADS);
     if (grid > 148 * 16) grid = 148 * 16;
     if (grid < 1) grid = 1;
-    nn_refine_kernel<<<grid, REFINE_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, (int)m.nm, m.geo, s.p64x, s.p64y, s.p64z,
-                                                      s.phx, s.phy, s.phz, (int)s.np, (int)s.np_pad, sc.n_splits,
-                                                      sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list, ctl,
-                                                      honor_done);
+    nn_refine_kernel<<<grid, REFINE_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.mhat, (int)m.nm, m.geo, s.p64x, s.p64y,
+                                                      s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)s.np_pad,
+                                                      sc.n_splits, sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list,
+                                                      sc.amb_thr, ctl, honor_done);
 }
 
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done, int sm_count,
-                     cudaStream_t st)
+                     cudaStream_t st, unsigned long long* trace)
 {
-    int grid = sm_count * 4;
-    if ((int64_t)grid > s.np) grid = (int)s.np;
-    if (grid < 1) grid = 1;
-    nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, (int)m.nm, s.p64x, s.p64y, s.p64z,
-                                                    sc.amb_list, s.idx, ctl, (int)s.np, honor_done);
+    const int grid = sm_count * 4;
+    nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.mhat, (int)m.nm, (int)m.nm_pad, s.p64x,
+                                                    s.p64y, s.p64z, s.phx, s.phy, s.phz, sc.amb_list, sc.amb_thr, s.idx,
+                                                    sc.seg_v, sc.seg_k, (int)sc.seg_cap, sc.batch_ticket, ctl,
+                                                    (int)s.np, honor_done, trace);
 }
+
+int nn_exact_batch_points() { return EX_P; }
 
 }  // namespace icpb

@@ -31,7 +31,7 @@ EXPORTS = [
     "icp_get_scene", "icp_reset_scene", "icp_closest", "icp_centroid", "icp_find_alignment", "icp_err_compute",
     "icp_get_transform", "icp_run", "icp_get_indices", "icp_get_stats", "icp_closest_matrix_host",
     "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
-    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world",
+    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run",
 ]
 
 
@@ -39,7 +39,8 @@ class IcpStats(C.Structure):
     _fields_ = [("np", C.c_int64), ("nm", C.c_int64), ("nn_calls", C.c_int64), ("nn_pairs", C.c_int64),
                 ("rerank_full", C.c_int64), ("rerank_chunk", C.c_int64), ("n_splits", C.c_int32),
                 ("tile_points", C.c_int32), ("chunk_points", C.c_int32), ("kernels_launched", C.c_int32),
-                ("ms_filter", C.c_float), ("ms_total", C.c_float)]
+                ("ms_filter", C.c_float), ("ms_total", C.c_float), ("ms_refine", C.c_float), ("ms_exact", C.c_float),
+                ("ms_align", C.c_float), ("reserved_", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -93,6 +94,11 @@ def load_library(path=None):
     L.icp_comm_unique_id.argtypes = [C.c_char_p, C.c_void_p]
     L.icp_comm_init.argtypes = [vp, C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     L.icp_comm_world.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icp_get_trace.argtypes = [vp, _dp]
+    L.icp_batch_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
+                                C.POINTER(C.c_int64), C.c_int, C.c_double, C.c_int, _ip, _dp, C.c_void_p, _dp]
+    L.icp_comm_peer_handle.argtypes = [vp, C.c_void_p]
+    L.icp_comm_peer_attach.argtypes = [vp, C.c_void_p, C.c_int, C.c_int]
     _lib = L
     return L
 
@@ -210,10 +216,54 @@ class Context:
         _ck(self._L.icp_get_stats(self._h, C.byref(st)))
         return st.as_dict()
 
+    def trace(self):
+        t = np.zeros(8)
+        _ck(self._L.icp_get_trace(self._h, _d(t)))
+        return t
+
     def comm_init(self, id128, rank, world, nccl_path=None):
         path = nccl_path or torch_nccl_path()
         buf = C.create_string_buffer(bytes(id128), 128)
         _ck(self._L.icp_comm_init(self._h, path.encode() if path else None, buf, int(rank), int(world)))
+
+
+    def comm_peer_handle(self):
+        """64-byte CUDA IPC handle of this rank's mailbox (all-gather these, then comm_peer_attach)."""
+        buf = C.create_string_buffer(64)
+        _ck(self._L.icp_comm_peer_handle(self._h, buf))
+        return buf.raw
+
+    def comm_peer_attach(self, handles, rank, world):
+        """handles: list of `world` 64-byte handles in rank order."""
+        blob = b"".join(handles)
+        assert len(blob) == 64 * world
+        buf = C.create_string_buffer(blob, len(blob))
+        _ck(self._L.icp_comm_peer_attach(self._h, buf, int(rank), int(world)))
+
+
+def batch_run(models, scenes, max_iter=30, threshold=1e-5, check_sizes=True, device=0, lanes=3, want_scene=True):
+    """Registers scenes[k] onto models[k] for every k (independent pairs, reference loop src/cpu.cc:55-79).
+    Returns dict(iters, err, srt[, new_p])."""
+    L = load_library()
+    n = len(models)
+    ms = [_pts(a) for a in models]
+    ps = [_pts(a) for a in scenes]
+    PP = C.POINTER(C.c_double) * max(n, 1)
+    mp = PP(*[_d(a) for a in ms])
+    pp = PP(*[_d(a) for a in ps])
+    nm = (C.c_int64 * max(n, 1))(*[len(a) for a in ms])
+    npts = (C.c_int64 * max(n, 1))(*[len(a) for a in ps])
+    iters = np.zeros(max(n, 1), dtype=np.int32)
+    err = np.zeros(max(n, 1))
+    srt = np.zeros((max(n, 1), 13))
+    outs = [np.empty_like(a) for a in ps] if want_scene else []
+    op = PP(*[_d(a) for a in outs]) if want_scene else None
+    _ck(L.icp_batch_run(int(device), int(lanes), n, mp, nm, pp, npts, int(max_iter), float(threshold),
+                        int(bool(check_sizes)), _i(iters), _d(err), op, _d(srt)))
+    res = dict(iters=iters[:n], err=err[:n], srt=srt[:n])
+    if want_scene:
+        res["new_p"] = outs
+    return res
 
 
 def shard_range(n, rank, world):

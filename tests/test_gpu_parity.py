@@ -80,6 +80,51 @@ def test_closest_near_ties_below_fp32_resolution(icp):
     assert np.array_equal(idx, idx_o)
 
 
+def test_closest_exact_scan_paths(icp):
+    # nn_exact work decomposition: (a) a handful of undecidable points against a model long enough to be cut
+    # into several segments (ragged last batch, cross-segment merge by ticket); (b) every scene point
+    # undecidable (one segment, many batches); (c) a scene far away from the model (large tau).
+    rng = np.random.default_rng(21)
+    base = rng.uniform(-1, 1, (20000, 3))
+    m = np.concatenate([base, base[:50][::-1]])           # 50 points exist twice, 20 000 indices apart
+    p = base[[3, 11, 17, 23, 29, 31, 47]] + 1e-10
+    idx_o, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
+    _, idx = icp.closest_matrix(p, m, return_index=True)
+    assert np.array_equal(idx, idx_o) and (idx < 50).all()
+    m2 = np.concatenate([base[:4500], base[:4500]])       # everything twice
+    p2 = base[rng.permutation(4500)[:1501]] - 1e-10
+    idx_o, _ = O.closest_matrix(p2, m2, O.NN_MULSQRT)
+    ctx = icp.Context(0)
+    ctx.set_model(m2)
+    ctx.set_scene(p2)
+    idx, _ = ctx.closest(want_Y=False)
+    assert np.array_equal(idx, idx_o) and (idx < 4500).all()
+    assert ctx.stats()["rerank_full"] == len(p2)
+    ctx.close()
+    p3 = rng.uniform(-1, 1, (3000, 3)) + np.array([40.0, -25.0, 60.0])
+    idx_o, _ = O.closest_matrix(p3, base, O.NN_MULSQRT)
+    _, idx = icp.closest_matrix(p3, base, return_index=True)
+    assert np.array_equal(idx, idx_o)
+
+
+def test_fused_alignment_equals_split_kernels(icp, clouds, monkeypatch):
+    # the cooperative K2+K3+K4 kernel and the separate moments / solve / transform kernels are the same maths
+    m, p = clouds("cow_ref"), clouds("cow_tr1")
+    res = []
+    for mode in ("fused", "split"):
+        monkeypatch.setenv("ICP_ALIGN", mode)
+        ctx = icp.Context(0)
+        ctx.set_model(m)
+        ctx.set_scene(p)
+        it, hist = ctx.run(30)
+        res.append((it, hist, ctx.get_scene(), ctx.transform(), ctx.stats()["kernels_launched"]))
+        ctx.close()
+    assert res[0][0] == res[1][0] == 7
+    assert res[0][4] < res[1][4]                           # 4 launches per iteration instead of 5
+    assert np.allclose(res[0][1], res[1][1], rtol=1e-9, atol=1e-18)
+    assert np.abs(res[0][2] - res[1][2]).max() < 1e-12
+
+
 @pytest.mark.parametrize("n,seed", [(1000, 0), (5000, 1), (65536, 2)])
 def test_closest_synthetic(icp, n, seed):
     m, p, _ = synthetic_pair(n, seed=seed)
