@@ -50,22 +50,34 @@ def load_cloud(name):
     return np.array([[float(x) for x in l.split(",")[:3]] for l in lines], dtype=np.float64)
 
 
-def synthetic(n, seed):
+def synthetic(n, seed, angle_deg=5.0):
     """model ~ U[-1,1]^3, scene = R m + t + 1e-3 noise, pseudo-randomly permuted."""
     rng = np.random.default_rng(seed)
     m = rng.uniform(-1.0, 1.0, (n, 3))
     ax = np.array([1.0, 2.0, 3.0]) / np.sqrt(14.0)
-    a = np.deg2rad(5.0)
+    a = np.deg2rad(angle_deg)
     K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
     R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
     p = m @ R.T + np.array([0.05, -0.03, 0.02]) + 1e-3 * rng.standard_normal((n, 3))
     return m, np.ascontiguousarray(p[rng.permutation(n)])
 
 
-def get_workload(name):
+def get_workload(name, max_iter=None):
+    m, p, it, chk, desc = _get_workload(name)
+    if max_iter:
+        it = max_iter
+        desc = desc.split(", max_iter")[0].split(", 10 iterations")[0] + f", max_iter {it}"
+    return m, p, it, chk, desc
+
+
+def _get_workload(name):
     if name in WORKLOADS:
         mn, pn, it, chk = WORKLOADS[name]
         return load_cloud(mn), load_cloud(pn), it, chk, f"{mn} vs {pn}, max_iter {it}"
+    if name.startswith("batch"):     # reference arm / CPU baseline of the batched workload: its first pair
+        n = {"batch64k": 1 << 16, "batch16k": 1 << 14}[name]
+        m, p = synthetic(n, 1000, angle_deg=2.0)
+        return m, p, 30, True, f"first pair of the batch: synthetic {n} points, rigid 2deg + 1e-3 noise, max_iter 30"
     n = SYNTHETIC[name]
     m, p = synthetic(n, 1000 + int(np.log2(n)))
     return m, p, 10, True, f"synthetic 2^{int(np.log2(n))} points, rigid 5deg + 1e-3 noise, 10 iterations"
@@ -139,7 +151,7 @@ def run_reference(args, rank, world):
     compiled) on the host cores, all threads, on a bounded sample of the same workload."""
     if rank != 0:
         return
-    m, p, max_iter, _, desc = get_workload(args.workload)
+    m, p, max_iter, _, desc = get_workload(args.workload, args.max_iter)
     sample_iters = 2 if len(m) * len(p) > 1e9 else max_iter
     if len(m) * len(p) > 1e11:      # synthetic >= 2^20: sample 4096 scene points against the full model
         p = p[:4096]
@@ -173,7 +185,9 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
-    m, p, max_iter, check, desc = get_workload(args.workload)
+    if args.workload.startswith('batch'):
+        return run_batch(args, rank, world, local_rank, torch, dist)
+    m, p, max_iter, check, desc = get_workload(args.workload, args.max_iter)
     if world > 1:
         check = False        # global scene = `world` shards of np points; the model stays nm points
 
@@ -234,7 +248,8 @@ def run_ours(args, rank, world, local_rank):
     # ---- end to end through the C-ABI with host buffers --------------------------------------------
     ctx2 = ctx
     e2e_t = []
-    for i in range(2 + args.steps):
+    e2e_reps = min(args.steps, 10)
+    for i in range(2 + e2e_reps):
         barrier()
         t0 = time.perf_counter()
         ctx2.set_model(m)
@@ -302,13 +317,77 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_batch(args, rank, world, local_rank, torch, dist):
+    """BASELINE config 5: many independent synthetic pairs, dealt round-robin to the GPUs (pair-per-GPU, nothing is
+    exchanged); on each GPU `lanes` contexts run concurrently (icp_batch_run).  A step registers every pair once,
+    through the C-ABI with HOST buffers (the batch entry point has no device-resident form), so value == e2e."""
+    import icp_b200
+    n = {"batch64k": 1 << 16, "batch16k": 1 << 14}[args.workload]
+    max_iter = args.max_iter or 30
+    mine = list(range(rank, args.pairs, world))
+    models, scenes = [], []
+    for k in mine:
+        m, p = synthetic(n, 1000 + k, angle_deg=2.0 + 6.0 * ((k * 37) % 101) / 100.0)
+        models.append(m)
+        scenes.append(p)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        return icp_b200.batch_run(models, scenes, max_iter=max_iter, device=local_rank, lanes=args.lanes, want_scene=True)
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        res = step()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = step()
+    torch.cuda.synchronize()
+    dt_local = time.perf_counter() - t0
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    evals_local = float(np.sum(res["iters"].astype(np.float64))) * n * n
+    tim = torch.tensor([dt_local], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([evals_local, float(np.sum(res["iters"]))], dtype=torch.float64, device="cuda")
+    if dist:
+        dist.all_reduce(tim, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        sec = tim.item() / args.steps
+        evals, iters = tot.tolist()
+        line = {"metric": "nn_distance_evals_per_sec", "value": evals / sec, "unit": "evals/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": sec * 1e3, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32 filter + f64 re-rank/alignment", "data": "synthetic",
+                "pairs_per_sec": args.pairs / sec, "icp_iterations_per_sec": iters / sec,
+                "config": {"workload": args.workload, "pairs": args.pairs, "points_per_cloud": n, "max_iter": max_iter,
+                           "lanes_per_gpu": args.lanes, "sharding": f"pair-per-GPU, {world} GPU(s), no communication",
+                           "l2": "each pair's clouds are uploaded from host memory inside the step (inputs > L2 in aggregate)"},
+                "roofline": None, "cpu_baseline": None,
+                "e2e": {"value": evals / sec, "unit": "evals/s", "h2d_bytes_per_step": args.pairs * 2 * n * 24,
+                        "d2h_bytes_per_step": args.pairs * (n * 24 + 13 * 8 + 12)},
+                "gpu_launches": int(iters) * 4 + args.pairs * 12, "clocks": clocks,
+                "mean_iterations_per_pair": iters / args.pairs}
+        print(json.dumps(line), flush=True)
+    if dist:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="horse", choices=list(WORKLOADS) + list(SYNTHETIC))
+    ap.add_argument("--workload", default="horse", choices=list(WORKLOADS) + list(SYNTHETIC) + ["batch64k", "batch16k"])
+    ap.add_argument("--max-iter", type=int, default=None, help="override the workload's max_iter")
+    ap.add_argument("--pairs", type=int, default=64, help="batch workloads: cloud pairs in total (dealt round-robin to the ranks)")
+    ap.add_argument("--lanes", type=int, default=3, help="batch workloads: concurrent contexts per GPU")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank holds a full copy of the scene as its shard (per-GPU work fixed); "
                          "strong = the one scene is cut into N contiguous blocks")

@@ -119,7 +119,8 @@ int icp_get_stats(icp_ctx* ctx, icp_stats* out);
 int icp_get_trace(icp_ctx* ctx, double out_us[8]);
 
 /* ---- stateless one-shot forms (host pointers in, host results out) — back the reference-shaped
- * wrappers of src/GPU/gpu.hh:110-116; each creates and destroys a context on device 0.
+ * wrappers of src/GPU/gpu.hh:110-116.  Stateless for the caller; internally each host thread keeps one hidden
+ * context on device 0 whose buffers are reused from call to call (creating one costs ~3 ms).
  * icp_closest_matrix_host   compute_Y_w_opti / CPU::closest_matrix
  * icp_nearest_index_host    compute_distance_w_naive(m, pi) -> int     src/GPU/compute.cu:279-308
  * icp_find_alignment_host   ICP::find_alignment(Y) on explicit pairs    src/cpu.cc:105-175, src/GPU/gpu.cc:95-151
@@ -128,6 +129,7 @@ int icp_get_trace(icp_ctx* ctx, double out_us[8]);
  * icp_y_p_norm_host         y_p_norm_w(y, p, n, d_caps, sp)             src/GPU/compute.cu:442-469 */
 int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np,
                             int32_t* idx_out, double* Y_xyz_out);
+void icp_release_cached(void);   /* frees the calling thread's hidden context (see above); optional */
 int icp_nearest_index_host(const double* m_xyz, int64_t nm, const double pi[3], int32_t* idx_out);
 int icp_find_alignment_host(const double* Y_xyz, const double* p_xyz, int64_t np, double* s, double R[9],
                             double t[3], double* err_align);

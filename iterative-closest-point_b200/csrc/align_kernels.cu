@@ -601,40 +601,72 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
 // ------------------------------------------------------------------------------------------------
 // Preparation kernels (run once per icp_set_model / icp_set_scene, not per iteration).
 
-// Bounding box of an AoS FP64 cloud: single block, out = min[3], max[3].
-__global__ void __launch_bounds__(1024) bbox_kernel(const double* __restrict__ xyz, int64_t n, double* __restrict__ out)
+// Bounding box of an AoS FP64 cloud: out = min[3], max[3].  Block partials -> the last block (ticket) folds them.
+constexpr int BBOX_THREADS = 512;
+__global__ void __launch_bounds__(BBOX_THREADS)
+bbox_kernel(const double* __restrict__ xyz, int64_t n, double* __restrict__ out, double* __restrict__ partials,
+            int* __restrict__ ticket)
 {
-    __shared__ double smin[3][32], smax[3][32];
+    __shared__ double smin[3][BBOX_THREADS / 32], smax[3][BBOX_THREADS / 32];
+    __shared__ int is_last;
     double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    auto block_minmax = [&]() {     // result valid in thread 0
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                mn[c] = fmin(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+                mx[c] = fmax(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+            }
+            if (lane == 0) { smin[c][w] = mn[c]; smax[c][w] = mx[c]; }
+        }
+        __syncthreads();
+        if (w == 0) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                double a = lane < BBOX_THREADS / 32 ? smin[c][lane] : 1e300;
+                double b = lane < BBOX_THREADS / 32 ? smax[c][lane] : -1e300;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    a = fmin(a, __shfl_xor_sync(0xffffffffu, a, o));
+                    b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+                }
+                mn[c] = a; mx[c] = b;
+            }
+        }
+        __syncthreads();
+    };
+    for (int64_t i = (int64_t)blockIdx.x * BBOX_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * BBOX_THREADS)
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const double v = xyz[3 * i + c];
             mn[c] = fmin(mn[c], v);
             mx[c] = fmax(mx[c], v);
         }
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    block_minmax();
+    if (threadIdx.x == 0) {
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            mn[c] = fmin(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
-            mx[c] = fmax(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
-        }
-        if (lane == 0) { smin[c][w] = mn[c]; smax[c][w] = mx[c]; }
+        for (int c = 0; c < 3; ++c) { partials[blockIdx.x * 6 + c] = mn[c]; partials[blockIdx.x * 6 + 3 + c] = mx[c]; }
+        __threadfence();
+        is_last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
     }
     __syncthreads();
-    if (w == 0) {
+    if (is_last) {
+        __threadfence();
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            double a = lane < (int)(blockDim.x >> 5) ? smin[c][lane] : 1e300;
-            double b = lane < (int)(blockDim.x >> 5) ? smax[c][lane] : -1e300;
+        for (int c = 0; c < 3; ++c) { mn[c] = 1e300; mx[c] = -1e300; }
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += BBOX_THREADS)
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                a = fmin(a, __shfl_xor_sync(0xffffffffu, a, o));
-                b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+            for (int c = 0; c < 3; ++c) {
+                mn[c] = fmin(mn[c], __ldcg(&partials[b * 6 + c]));
+                mx[c] = fmax(mx[c], __ldcg(&partials[b * 6 + 3 + c]));
             }
-            if (lane == 0) { out[c] = a; out[3 + c] = b; }
+        block_minmax();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { out[c] = mn[c]; out[3 + c] = mx[c]; }
+            *ticket = 0;
         }
     }
 }
@@ -844,9 +876,13 @@ void launch_finish(const double* err_sum, double n_global, double threshold, dou
     finish_kernel<<<1, 1, 0, st>>>(err_sum, n_global, threshold, err_hist, ctl);
 }
 
-void launch_bbox(const double* xyz_aos, int64_t n, double* out_min3_max3, cudaStream_t st)
+void launch_bbox(const double* xyz_aos, int64_t n, double* out_min3_max3, double* partials, int max_blocks, int* ctl,
+                 cudaStream_t st)
 {
-    bbox_kernel<<<1, 1024, 0, st>>>(xyz_aos, n, out_min3_max3);
+    int64_t blocks = (n + BBOX_THREADS * 4 - 1) / (BBOX_THREADS * 4);
+    if (blocks > max_blocks) blocks = max_blocks;
+    if (blocks < 1) blocks = 1;
+    bbox_kernel<<<(int)blocks, BBOX_THREADS, 0, st>>>(xyz_aos, n, out_min3_max3, partials, ctl + CTL_TICKET_BBOX);
 }
 
 void launch_model_geo(double* geo, cudaStream_t st) { model_geo_kernel<<<1, 1, 0, st>>>(geo); }

@@ -103,6 +103,7 @@ struct icp_ctx {
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
     int forced_splits = 0;
+    size_t cap_nm = 0, cap_np = 0;         // allocated capacities (points): buffers only ever grow
     // fused alignment kernel (cooperative) and the peer-memory exchange it carries when world > 1
     int align_blocks_max = 148;
     PeerMailbox* d_mailbox = nullptr;
@@ -335,10 +336,13 @@ int icp_set_model(icp_ctx* c, const double* m_xyz, int64_t nm)
     CK(cudaMemcpyAsync(c->d_stage, m_xyz, (size_t)nm * 3 * sizeof(double), cudaMemcpyHostToDevice, c->st));
     c->m.nm = nm;
     c->m.nm_pad = (nm + NN_TM - 1) / NN_TM * NN_TM;
-    if ((r = dalloc(&c->m.m64x, (size_t)nm)) || (r = dalloc(&c->m.m64y, (size_t)nm)) ||
-        (r = dalloc(&c->m.m64z, (size_t)nm)) || (r = dalloc(&c->m.mhat, (size_t)c->m.nm_pad)))
-        return r;
-    launch_bbox(c->d_stage, nm, c->m.geo + 4, c->st);
+    if (c->cap_nm < (size_t)c->m.nm_pad) {       // grow only: cudaFree/cudaMalloc synchronise the whole device
+        if ((r = dalloc(&c->m.m64x, (size_t)c->m.nm_pad)) || (r = dalloc(&c->m.m64y, (size_t)c->m.nm_pad)) ||
+            (r = dalloc(&c->m.m64z, (size_t)c->m.nm_pad)) || (r = dalloc(&c->m.mhat, (size_t)c->m.nm_pad)))
+            return r;
+        c->cap_nm = (size_t)c->m.nm_pad;
+    }
+    launch_bbox(c->d_stage, nm, c->m.geo + 4, c->d_partials, c->sm_count * 2, c->d_ctl, c->st);
     launch_model_geo(c->m.geo, c->st);
     launch_model_build(c->d_stage, c->m, c->st);
     CK(cudaGetLastError());
@@ -359,19 +363,20 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
     if ((r = ensure_stage(c, (size_t)np * 3 + 8))) return r;
     CK(cudaMemcpyAsync(c->d_stage, p_xyz, (size_t)np * 3 * sizeof(double), cudaMemcpyHostToDevice, c->st));
     const int64_t np_pad = (np + NN_TILE - 1) / NN_TILE * NN_TILE;
-    if (c->s.np != np || !c->s.p64x) {
-        c->s.np = np; c->s.np_pad = np_pad;
-        if ((r = dalloc(&c->s.p64x, (size_t)np)) || (r = dalloc(&c->s.p64y, (size_t)np)) ||
-            (r = dalloc(&c->s.p64z, (size_t)np)) || (r = dalloc(&c->s.q64x, (size_t)np)) ||
-            (r = dalloc(&c->s.q64y, (size_t)np)) || (r = dalloc(&c->s.q64z, (size_t)np)) ||
+    c->s.np = np; c->s.np_pad = np_pad;
+    if (c->cap_np < (size_t)np_pad) {            // grow only
+        c->cap_np = (size_t)np_pad;
+        if ((r = dalloc(&c->s.p64x, (size_t)np_pad)) || (r = dalloc(&c->s.p64y, (size_t)np_pad)) ||
+            (r = dalloc(&c->s.p64z, (size_t)np_pad)) || (r = dalloc(&c->s.q64x, (size_t)np_pad)) ||
+            (r = dalloc(&c->s.q64y, (size_t)np_pad)) || (r = dalloc(&c->s.q64z, (size_t)np_pad)) ||
             (r = dalloc(&c->s.phx, (size_t)np_pad)) || (r = dalloc(&c->s.phy, (size_t)np_pad)) ||
-            (r = dalloc(&c->s.phz, (size_t)np_pad)) || (r = dalloc(&c->s.perm, (size_t)np)) ||
-            (r = dalloc(&c->s.idx, (size_t)np)) || (r = dalloc(&c->sc.amb_list, (size_t)np)) ||
-            (r = dalloc(&c->sc.amb_thr, (size_t)np)))
+            (r = dalloc(&c->s.phz, (size_t)np_pad)) || (r = dalloc(&c->s.perm, (size_t)np_pad)) ||
+            (r = dalloc(&c->s.idx, (size_t)np_pad)) || (r = dalloc(&c->sc.amb_list, (size_t)np_pad)) ||
+            (r = dalloc(&c->sc.amb_thr, (size_t)np_pad)))
             return r;
         // nn_exact scratch: per (model segment, queued point) minima + one ticket per batch of queued points
-        c->sc.seg_cap = (size_t)np + 65536;
-        const size_t n_tickets = (size_t)np / nn_exact_batch_points() + 2;
+        c->sc.seg_cap = (size_t)np_pad + 65536;
+        const size_t n_tickets = (size_t)np_pad / nn_exact_batch_points() + 2;
         if ((r = dalloc(&c->sc.seg_v, c->sc.seg_cap)) || (r = dalloc(&c->sc.seg_k, c->sc.seg_cap)) ||
             (r = dalloc(&c->sc.batch_ticket, n_tickets)))
             return r;
@@ -391,7 +396,7 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
         c->sort_cap = (size_t)np;
     }
     double* bbox = c->d_stage + (size_t)np * 3;
-    launch_bbox(c->d_stage, np, bbox, c->st);
+    launch_bbox(c->d_stage, np, bbox, c->d_partials, c->sm_count * 2, c->d_ctl, c->st);
     launch_scene_keys(c->d_stage, np, bbox, c->d_keys, c->d_vals, c->st);
     size_t bytes = c->cub_bytes;
     CK(cub::DeviceRadixSort::SortPairs(c->d_cub, bytes, c->d_keys, c->d_keys_alt, c->d_vals, c->s.perm, (int)np, 0, 30,
@@ -670,15 +675,37 @@ int icp_get_stats(icp_ctx* c, icp_stats* out)
 }
 
 // ---- stateless one-shot forms (src/GPU/gpu.hh:110-116) -------------------------------------------
+// "Stateless" as seen by the caller (host matrices in, host results out, nothing to keep), like the
+// reference's wrappers which allocate and free device memory on every call (src/GPU/compute.cu:154-245).
+// Creating a context costs ~3 ms (stream, events, a dozen cudaMalloc), thirty times the work of a cow-sized
+// call, so each host thread keeps ONE hidden context for these entry points and reuses its buffers.
+// icp_release_cached() frees the calling thread's hidden context.
+
+static thread_local icp_ctx* t_oneshot = nullptr;
+
+static int oneshot_ctx(icp_ctx** out)
+{
+    if (!t_oneshot) {
+        int r = icp_create(&t_oneshot, 0);
+        if (r) { t_oneshot = nullptr; return r; }
+    }
+    *out = t_oneshot;
+    return ICP_OK;
+}
+
+void icp_release_cached(void)
+{
+    if (t_oneshot) icp_destroy(t_oneshot);
+    t_oneshot = nullptr;
+}
 
 int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np, int32_t* idx_out,
                             double* Y_out)
 {
     icp_ctx* c = nullptr;
-    int r = icp_create(&c, 0);
+    int r = oneshot_ctx(&c);
     if (r) return r;
     if (!(r = icp_set_model(c, m_xyz, nm)) && !(r = icp_set_scene(c, p_xyz, np))) r = icp_closest(c, idx_out, Y_out);
-    icp_destroy(c);
     return r;
 }
 
@@ -691,13 +718,12 @@ int icp_nearest_index_host(const double* m_xyz, int64_t nm, const double pi[3], 
 static int pair_ctx(icp_ctx** out, const double* Y_xyz, const double* p_xyz, int64_t n)
 {
     icp_ctx* c = nullptr;
-    int r = icp_create(&c, 0);
+    int r = oneshot_ctx(&c);
     if (r) return r;
-    if ((r = icp_set_model(c, Y_xyz, n)) || (r = icp_set_scene(c, p_xyz, n))) { icp_destroy(c); return r; }
+    if ((r = icp_set_model(c, Y_xyz, n)) || (r = icp_set_scene(c, p_xyz, n))) return r;
     // sorted position i holds original point perm[i], whose partner is Y[perm[i]]
     if (cudaMemcpyAsync(c->s.idx, c->s.perm, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToDevice, c->st) != cudaSuccess) {
         g_err = "pair_ctx: copy failed";
-        icp_destroy(c);
         return ICP_ERR_CUDA;
     }
     c->have_idx = true;
@@ -719,12 +745,10 @@ int icp_err_compute_host(const double* Y_xyz, double* p_xyz, int64_t np, int in_
     if (cudaMemcpyAsync(c->d_xf, xf, sizeof(xf), cudaMemcpyHostToDevice, c->st) != cudaSuccess ||
         cudaStreamSynchronize(c->st) != cudaSuccess) {
         g_err = "icp_err_compute_host: upload failed";
-        icp_destroy(c);
         return ICP_ERR_CUDA;
     }
     r = icp_err_compute(c, in_place, err);
     if (!r && in_place) r = icp_get_scene(c, p_xyz);
-    icp_destroy(c);
     return r;
 }
 
@@ -735,24 +759,22 @@ int icp_find_alignment_host(const double* Y_xyz, const double* p_xyz, int64_t np
     icp_ctx* c = nullptr;
     int r = pair_ctx(&c, Y_xyz, p_xyz, np);
     if (r) return r;
-    r = icp_find_alignment(c, s, R, t, err_align);
-    icp_destroy(c);
-    return r;
+    return icp_find_alignment(c, s, R, t, err_align);
 }
 
 int icp_subtract_col_host(const double* M_xyz, int64_t n, const double m[3], double* out_xyz)
 {
     if (!M_xyz || !m || !out_xyz || n < 1) { g_err = "icp_subtract_col_host: bad arguments"; return ICP_ERR_INVALID; }
     icp_ctx* c = nullptr;
-    int r = icp_create(&c, 0);
+    int r = oneshot_ctx(&c);
     if (r) return r;
-    if ((r = ensure_stage(c, (size_t)n * 6))) { icp_destroy(c); return r; }
+    CK(cudaSetDevice(c->device));
+    if ((r = ensure_stage(c, (size_t)n * 6))) return r;
     cudaError_t e = cudaMemcpyAsync(c->d_stage, M_xyz, (size_t)n * 24, cudaMemcpyHostToDevice, c->st);
     launch_subtract_col(c->d_stage, n, m[0], m[1], m[2], c->d_stage + (size_t)n * 3, c->st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(out_xyz, c->d_stage + (size_t)n * 3, (size_t)n * 24, cudaMemcpyDeviceToHost, c->st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
     if (e != cudaSuccess) { g_err = std::string("icp_subtract_col_host: ") + cudaGetErrorString(e); r = ICP_ERR_CUDA; }
-    icp_destroy(c);
     return r;
 }
 
@@ -767,12 +789,11 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
     cudaError_t e = cudaMemcpyAsync(mom, c->d_mom, sizeof(mom), cudaMemcpyDeviceToHost, c->st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(geo, c->m.geo, sizeof(geo), cudaMemcpyDeviceToHost, c->st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
-    if (e != cudaSuccess) { g_err = std::string("icp_y_p_norm_host: ") + cudaGetErrorString(e); icp_destroy(c); return ICP_ERR_CUDA; }
+    if (e != cudaSuccess) { g_err = std::string("icp_y_p_norm_host: ") + cudaGetErrorString(e); return ICP_ERR_CUDA; }
     // sums were taken about c0: |v|^2 = |a|^2 + 2 c0.a + |c0|^2
     const double c2 = geo[0] * geo[0] + geo[1] * geo[1] + geo[2] * geo[2];
     if (sp) *sp = mom[16] + 2.0 * (geo[0] * mom[1] + geo[1] * mom[2] + geo[2] * mom[3]) + (double)n * c2;
     if (d_caps) *d_caps = mom[17] + 2.0 * (geo[0] * mom[4] + geo[1] * mom[5] + geo[2] * mom[6]) + (double)n * c2;
-    icp_destroy(c);
     return ICP_OK;
 }
 

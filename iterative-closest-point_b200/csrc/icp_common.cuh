@@ -30,7 +30,7 @@ constexpr int XF_N  = 20;   // s, R[9], t[3], mu_p[3], mu_y[3], spare
 
 // ctl[] slots (int32, device)
 enum { CTL_DONE = 0, CTL_ITERS = 1, CTL_AMB_COUNT = 2, CTL_TICKET_MOM = 3, CTL_TICKET_ERR = 4,
-       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_TICKET_NN = 7, CTL_COMM_TIMEOUT = 8, CTL_N = 12 };
+       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_TICKET_NN = 7, CTL_COMM_TIMEOUT = 8, CTL_TICKET_BBOX = 9, CTL_N = 12 };
 
 // ---- peer-memory exchange (multi-GPU, one process per GPU) ---------------------------------------
 // Every rank owns one mailbox in its HBM, mapped into all peers through CUDA IPC.  An exchange with
@@ -117,7 +117,8 @@ void launch_finish(const double* err_sum, double n_global, double threshold, dou
                    cudaStream_t st);
 
 // preparation
-void launch_bbox(const double* xyz_aos, int64_t n, double* out_min3_max3, cudaStream_t st);
+void launch_bbox(const double* xyz_aos, int64_t n, double* out_min3_max3, double* partials /* >= 6 * max_blocks */,
+                 int max_blocks, int* ctl, cudaStream_t st);
 void launch_model_geo(double* geo, cudaStream_t st);   // geo[4..9] bbox -> geo[0..3] = c0, Rm
 void launch_model_build(const double* xyz_aos, const ModelDev& m, cudaStream_t st);
 void launch_scene_keys(const double* xyz_aos, int64_t n, const double* bbox, uint32_t* keys, int32_t* vals,

@@ -9,14 +9,14 @@
 #include "load.hh"
 
 #include <cctype>
+#include <charconv>
 #include <cstdio>
-#include <fstream>
 #include <string>
 
 namespace {
 
-// Emulates sscanf(line, "%lf,%lf,%lf", &x, &y, &z) on [s, e).
-void parse3(const char* s, const char* e, double out[3])
+// Emulates sscanf(line, "%lf,%lf,%lf", &x, &y, &z) on [s, e): the general (slow) form.
+void parse3_general(const char* s, const char* e, double out[3])
 {
     out[0] = out[1] = out[2] = 0.0;
     std::string tmp(s, e);               // NUL-terminated copy so strtod cannot run past the line
@@ -30,6 +30,24 @@ void parse3(const char* s, const char* e, double out[3])
         c = end;
         if (k < 2) {
             if (*c != ',') return;
+            ++c;
+        }
+    }
+}
+
+// Fast path: three plain decimal fields parsed in place with std::from_chars (bounded by the line, no
+// copy, no locale).  Anything from_chars does not take exactly like sscanf's %lf (leading blanks or '+',
+// inf/nan, hex floats, a short line) goes through parse3_general, so the observable result is unchanged.
+void parse3(const char* s, const char* e, double out[3])
+{
+    const char* c = s;
+    for (int k = 0; k < 3; ++k) {
+        if (c >= e || !(std::isdigit((unsigned char)*c) || *c == '-' || *c == '.')) return parse3_general(s, e, out);
+        const auto r = std::from_chars(c, e, out[k]);
+        if (r.ec != std::errc()) return parse3_general(s, e, out);
+        c = r.ptr;
+        if (k < 2) {
+            if (c >= e || *c != ',') return parse3_general(s, e, out);
             ++c;
         }
     }
@@ -77,11 +95,20 @@ GPU::Matrix load_matrix(const char* filename)
 
 void write_matrix_to(const GPU::Matrix& matrix, const char* filename)
 {
-    std::ofstream output(filename);
-    output << "Points_0,Points_1,Points_2" << std::endl;
-    for (long i = 0; i < matrix.cols(); i++)
-        output << matrix(0, i) << ',' << matrix(1, i) << ',' << matrix(2, i) << '\n';
-    output.flush();
+    // default ostream formatting of a double == printf("%g") (6 significant digits): src/load.cc:71-79
+    std::FILE* f = std::fopen(filename, "wb");
+    if (f) {
+        std::string buf;
+        buf.reserve((size_t)matrix.cols() * 40 + 64);
+        buf += "Points_0,Points_1,Points_2\n";
+        char line[128];
+        for (long i = 0; i < matrix.cols(); i++) {
+            const int n = std::snprintf(line, sizeof(line), "%g,%g,%g\n", matrix(0, i), matrix(1, i), matrix(2, i));
+            buf.append(line, (size_t)n);
+        }
+        std::fwrite(buf.data(), 1, buf.size(), f);
+        std::fclose(f);
+    }
     std::cerr << "[output] output file \"" << filename << "\" was generated." << std::endl;
 }
 

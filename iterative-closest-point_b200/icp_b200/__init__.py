@@ -31,7 +31,7 @@ EXPORTS = [
     "icp_get_scene", "icp_reset_scene", "icp_closest", "icp_centroid", "icp_find_alignment", "icp_err_compute",
     "icp_get_transform", "icp_run", "icp_get_indices", "icp_get_stats", "icp_closest_matrix_host",
     "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
-    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run",
+    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run", "icp_release_cached",
 ]
 
 

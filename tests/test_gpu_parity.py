@@ -125,6 +125,24 @@ def test_fused_alignment_equals_split_kernels(icp, clouds, monkeypatch):
     assert np.abs(res[0][2] - res[1][2]).max() < 1e-12
 
 
+def test_batch_run_matches_oracle_per_pair(icp):
+    # BASELINE config 5 in miniature: independent pairs through icp_batch_run, 3 concurrent lanes
+    models, scenes = [], []
+    for k in range(7):
+        m, p, _ = synthetic_pair(1500 + 211 * k, seed=100 + k, angle_deg=2.0 + k, noise=1e-3 if k % 2 else 0.0)
+        models.append(m)
+        scenes.append(p)
+    res = icp.batch_run(models, scenes, max_iter=25, lanes=3)
+    for k in range(7):
+        ro = O.icp_run(models[k], scenes[k], 25)
+        assert res["iters"][k] == ro["iters"], k
+        assert abs(res["err"][k] - ro["err"][-1]) <= 1e-5 * abs(ro["err"][-1]) + 1e-18
+        assert np.abs(res["new_p"][k] - ro["new_p"]).max() < 1e-9
+    # error path: a size mismatch in one pair fails the batch like the reference's exit(-1)
+    with pytest.raises(icp.IcpError):
+        icp.batch_run([models[0]], [scenes[1]], max_iter=5)
+
+
 @pytest.mark.parametrize("n,seed", [(1000, 0), (5000, 1), (65536, 2)])
 def test_closest_synthetic(icp, n, seed):
     m, p, _ = synthetic_pair(n, seed=seed)
