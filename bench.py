@@ -163,7 +163,7 @@ def run_reference(args, rank, world):
             vals.append((v, it, dt))
     value = float(np.mean([v for v, _, _ in vals]))
     ms = float(np.mean([dt for _, _, dt in vals])) * 1e3
-    sample = f"{sample_iters} ICP iteration(s) of {desc} ({len(p)} scene x {len(m)} model points) per step"
+    sample = f"{vals[-1][1]} ICP iteration(s) of {desc} ({len(p)} scene x {len(m)} model points) per step"
     line = {"impl": "reference", "metric": "nn_distance_evals_per_sec", "value": value, "unit": "evals/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "reference clouds",

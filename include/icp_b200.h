@@ -129,7 +129,7 @@ int icp_get_trace(icp_ctx* ctx, double out_us[8]);
  * icp_y_p_norm_host         y_p_norm_w(y, p, n, d_caps, sp)             src/GPU/compute.cu:442-469 */
 int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np,
                             int32_t* idx_out, double* Y_xyz_out);
-void icp_release_cached(void);   /* frees the calling thread's hidden context (see above); optional */
+void icp_release_cached(void);   /* frees the calling thread's hidden context and icp_batch_run's idle lane contexts; optional */
 int icp_nearest_index_host(const double* m_xyz, int64_t nm, const double pi[3], int32_t* idx_out);
 int icp_find_alignment_host(const double* Y_xyz, const double* p_xyz, int64_t np, double* s, double R[9],
                             double t[3], double* err_align);

@@ -102,7 +102,7 @@ struct icp_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
-    int forced_splits = 0;
+    int forced_ctas = 0;
     size_t cap_nm = 0, cap_np = 0;         // allocated capacities (points): buffers only ever grow
     // fused alignment kernel (cooperative) and the peer-memory exchange it carries when world > 1
     int align_blocks_max = 148;
@@ -125,32 +125,26 @@ int ensure_stage(icp_ctx* c, size_t doubles)
     return ICP_OK;
 }
 
-// 2-D decomposition: choose the number of model splits so that the CTAs balance over the SMs.
+// Stream-K decomposition of the filter (see nn_filter_kernel): the grid is a whole number of waves of
+// 4 CTAs per SM, each CTA owning an equal contiguous range of chunk-units.  One wave while a CTA's range stays
+// below ~1024 chunks (horse: 61.6 chunks per CTA); beyond that, more waves of ~1024-chunk ranges, so that the
+// hardware's dynamic block scheduling evens out SM-to-SM speed differences on long runs (measured on 2^20
+// points: a single wave of 28 000-chunk ranges is 1.9 % slower than 28 waves).  Never so many CTAs that one
+// gets less than a staged model tile (8 chunks).  n_splits = the most partial results a scene tile can receive.
 void choose_splits(icp_ctx* c)
 {
-    const int n_tiles = (int)(c->s.np_pad / NN_TILE);
-    const int nm_tiles = (int)(c->m.nm_pad / NN_TM);
-    int best_S = 1, best_tps = nm_tiles;
-    double best_cost = 1e300;
-    const int max_S = nm_tiles < 64 ? nm_tiles : 64;
-    for (int S = 1; S <= max_S; ++S) {
-        const int tps = (nm_tiles + S - 1) / S;
-        const int S_eff = (nm_tiles + tps - 1) / tps;
-        if (S_eff != S) continue;
-        const long items = (long)n_tiles * S_eff;
-        const long per_sm = (items + c->sm_count - 1) / c->sm_count;
-        // one CTA per SM leaves a single warp per scheduler: penalise it mildly
-        const double occ_pen = per_sm >= 3 ? 1.0 : (per_sm == 2 ? 1.05 : 1.25);
-        const double cost = (double)per_sm * (tps + 0.5) * occ_pen;
-        if (cost < best_cost - 1e-9) { best_cost = cost; best_S = S_eff; best_tps = tps; }
-    }
-    if (c->forced_splits > 0) {
-        int S = c->forced_splits < nm_tiles ? c->forced_splits : nm_tiles;
-        best_tps = (nm_tiles + S - 1) / S;
-        best_S = (nm_tiles + best_tps - 1) / best_tps;
-    }
-    c->sc.n_splits = best_S;
-    c->sc.tiles_per_split = best_tps;
+    const long long n_tiles = c->s.np_pad / NN_TILE;
+    const long long cpt = c->m.nm_pad / NN_G;
+    const long long total = n_tiles * cpt;
+    const long long wave = (long long)c->sm_count * 4;
+    long long waves = (total + 1024 * wave - 1) / (1024 * wave);
+    if (waves < 1) waves = 1;
+    long long n_cta = wave * waves;
+    if (c->forced_ctas > 0) n_cta = c->forced_ctas;
+    if (n_cta > total / 8) n_cta = total / 8;
+    if (n_cta < 1) n_cta = 1;
+    c->sc.n_cta = (int)n_cta;
+    c->sc.n_splits = (int)((n_cta + n_tiles - 1) / n_tiles + 1);
 }
 
 int ensure_scratch(icp_ctx* c)
@@ -296,7 +290,7 @@ int icp_create(icp_ctx** out, int device)
     if (const char* e = getenv("ICP_ALIGN")) c->align_fused = !strcmp(e, "fused");
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
-    if (const char* e = getenv("ICP_NN_SPLITS")) c->forced_splits = atoi(e);
+    if (const char* e = getenv("ICP_NN_CTAS")) c->forced_ctas = atoi(e);
     if ((r = set_identity_xf(c))) { delete c; return r; }
     *out = c;
     return ICP_OK;
@@ -693,10 +687,13 @@ static int oneshot_ctx(icp_ctx** out)
     return ICP_OK;
 }
 
+static void lane_pool_clear();
+
 void icp_release_cached(void)
 {
     if (t_oneshot) icp_destroy(t_oneshot);
     t_oneshot = nullptr;
+    lane_pool_clear();
 }
 
 int icp_closest_matrix_host(const double* m_xyz, int64_t nm, const double* p_xyz, int64_t np, int32_t* idx_out,
@@ -802,6 +799,28 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
 // stream) on `device` and pull pairs from a shared counter.  While one lane is in the latency-bound
 // tail of an iteration (refine / exact / alignment) or copying over PCIe, the other lanes' filter
 // kernels keep the SMs busy.  Across GPUs the launcher deals pairs round-robin, one process per GPU.
+// Pool of idle lane contexts per device (icp_release_cached() empties it).
+static std::mutex g_pool_mu;
+static std::vector<std::pair<int, icp_ctx*>> g_pool;
+
+static icp_ctx* lane_pool_take(int device)
+{
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    for (size_t i = 0; i < g_pool.size(); ++i)
+        if (g_pool[i].first == device) {
+            icp_ctx* c = g_pool[i].second;
+            g_pool.erase(g_pool.begin() + (long)i);
+            return c;
+        }
+    return nullptr;
+}
+
+static void lane_pool_give(int device, icp_ctx* c)
+{
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    g_pool.emplace_back(device, c);
+}
+
 int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
                   const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
                   int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out)
@@ -815,8 +834,8 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     std::mutex mu;
     std::string first_err;
     auto worker = [&]() {
-        icp_ctx* c = nullptr;
-        int r = icp_create(&c, device);
+        icp_ctx* c = lane_pool_take(device);       // contexts survive between calls: no per-call cudaMalloc storm
+        int r = c ? ICP_OK : icp_create(&c, device);
         std::vector<double> hist((size_t)(max_iter > 0 ? max_iter : 1));
         while (!r && status.load() == ICP_OK) {
             const int64_t k = next.fetch_add(1);
@@ -834,13 +853,20 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
             std::lock_guard<std::mutex> lk(mu);
             if (status.load() == ICP_OK) { status.store(r); first_err = g_err; }
         }
-        if (c) icp_destroy(c);
+        if (c) lane_pool_give(device, c);
     };
     std::vector<std::thread> th;
     for (int i = 0; i < lanes; ++i) th.emplace_back(worker);
     for (auto& t : th) t.join();
     if (status.load() != ICP_OK) g_err = first_err;
     return status.load();
+}
+
+static void lane_pool_clear()
+{
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    for (auto& e : g_pool) icp_destroy(e.second);
+    g_pool.clear();
 }
 
 // ---- multi-GPU ----------------------------------------------------------------------------------

@@ -66,8 +66,8 @@ struct SceneDev {
 };
 
 struct NNScratch {
-    int n_splits = 0;
-    int tiles_per_split = 0;     // in units of NN_TM model points
+    int n_cta = 0;               // CTAs of the filter's single wave (stream-K decomposition)
+    int n_splits = 0;            // max partial results ("slots") any scene tile receives
     float* best = nullptr;       // [n_splits][np_pad]
     float* runner = nullptr;
     uint32_t* chunk = nullptr;

@@ -79,9 +79,20 @@ constexpr int SOA_BUF = 4 * SOA_PLANE;                 // floats per buffer (X|Y
 constexpr size_t FILTER_SMEM = NN_TM * sizeof(float4) + 2 * SOA_BUF * sizeof(float);
 
 // ------------------------------------------------------------------------------------------------
+// Work decomposition ("stream-K"): the np_pad/1024 scene tiles x cpt model chunks (64 points each) form one
+// linear sequence of T = n_tiles * cpt chunk-units, scene tile major.  The grid is ONE wave of CTAs (4 per SM)
+// and CTA b owns the contiguous range [b*T/n, (b+1)*T/n): every CTA gets the same work to within one chunk,
+// whatever the cloud sizes, so all SMs finish together.  A range may end inside a scene tile and continue in
+// the next one; each (CTA, scene tile) segment writes its own partial result into slot = b - first CTA of that
+// tile, and nn_refine merges a tile's slots (slot_range() gives their number from the same arithmetic).
+__device__ __forceinline__ int cta_of_unit(long long x, long long T, int n)      // the CTA whose range holds unit x
+{
+    return (int)(((x + 1) * n - 1) / T);
+}
+
 __global__ void __launch_bounds__(NN_THREADS, 4)
 nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx, const float* __restrict__ phy,
-                 const float* __restrict__ phz, int np_pad, int n_splits, int tiles_per_split, int nm_tiles,
+                 const float* __restrict__ phz, int np_pad, int n_tiles, int cpt,
                  float* __restrict__ out_best, float* __restrict__ out_runner, uint32_t* __restrict__ out_chunk,
                  const int* __restrict__ ctl, int honor_done)
 {
@@ -93,114 +104,135 @@ nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx,
     __shared__ __align__(8) uint64_t mbar;
 
     const int tid = threadIdx.x;
-    const int tile = blockIdx.x / n_splits;
-    const int split = blockIdx.x - tile * n_splits;
-    const int mt0 = split * tiles_per_split;
-    const int mt1 = min(mt0 + tiles_per_split, nm_tiles);
-    const int pbase = tile * NN_TILE;
+    constexpr int CPM = NN_TM / NN_G;                       // chunks per staged model tile (8)
+    // this CTA's range, reduced to 32-bit loop state: (tile, c_lo, remaining)
+    int tile, c_lo, remaining;
+    {
+        const long long T = (long long)n_tiles * cpt;
+        const long long begin = (long long)blockIdx.x * T / (long long)gridDim.x;
+        const long long end = (long long)(blockIdx.x + 1) * T / (long long)gridDim.x;
+        tile = (int)(begin / cpt);
+        c_lo = (int)(begin - (long long)tile * cpt);
+        remaining = (int)(end - begin);
+    }
 
     if (tid == 0) {
         mbar_init(&mbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (tid == 0 && mt0 < mt1) {
-        mbar_expect_tx(&mbar, NN_TM * sizeof(float4));
-        bulk_g2s(raw, mhat + (size_t)mt0 * NN_TM, NN_TM * sizeof(float4), &mbar);
-    }
-
-    // CTA-local origin: the middle point of the (Morton-sorted) scene tile.
-    const float cx = phx[pbase + NN_TILE / 2], cy = phy[pbase + NN_TILE / 2], cz = phz[pbase + NN_TILE / 2];
-
-    float2 ax[NN_R], ay[NN_R], az[NN_R];
-    float best[NN_R], runner[NN_R];
-    uint32_t bchunk[NN_R];
-#pragma unroll
-    for (int r = 0; r < NN_R; ++r) {
-        const int j = pbase + r * NN_THREADS + tid;
-        const float x = -2.0f * __fsub_rn(phx[j], cx);
-        const float y = -2.0f * __fsub_rn(phy[j], cy);
-        const float z = -2.0f * __fsub_rn(phz[j], cz);
-        ax[r] = make_float2(x, x);
-        ay[r] = make_float2(y, y);
-        az[r] = make_float2(z, z);
-        best[r] = __int_as_float(0x7f800000);
-        runner[r] = __int_as_float(0x7f800000);
-        bchunk[r] = 0u;
-    }
-
     uint32_t parity = 0;
-    for (int mt = mt0; mt < mt1; ++mt) {
-        float* buf = soa + ((mt - mt0) & 1) * SOA_BUF;
-        // ---- stage: raw float4 (TMA) -> CTA-local SoA planes --------------------------------------
-        mbar_wait(&mbar, parity);
-        parity ^= 1u;
-#pragma unroll
-        for (int k = 0; k < NN_TM / NN_THREADS; ++k) {
-            const int i = k * NN_THREADS + tid;
-            const float4 v = raw[i];
-            const float x = __fsub_rn(v.x, cx), y = __fsub_rn(v.y, cy), z = __fsub_rn(v.z, cz);
-            buf[i] = x;
-            buf[SOA_PLANE + i] = y;
-            buf[2 * SOA_PLANE + i] = z;
-            buf[3 * SOA_PLANE + i] = __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x)));
-        }
-        __syncthreads();   // planes visible; everyone is done with `raw` and with the other buffer
-        if (tid == 0 && mt + 1 < mt1) {
+
+    while (remaining > 0) {
+        // ---- one (CTA, scene tile) segment: model chunks [c_lo, c_hi) of scene tile `tile` ------------
+        const int c_hi = min(cpt, c_lo + remaining);
+        const int slot = (int)blockIdx.x - cta_of_unit((long long)tile * cpt, (long long)n_tiles * cpt, (int)gridDim.x);
+        const int mt0 = c_lo / CPM, mt1 = (c_hi + CPM - 1) / CPM;
+        const int pbase = tile * NN_TILE;
+
+        if (tid == 0) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_expect_tx(&mbar, NN_TM * sizeof(float4));
-            bulk_g2s(raw, mhat + (size_t)(mt + 1) * NN_TM, NN_TM * sizeof(float4), &mbar);
+            bulk_g2s(raw, mhat + (size_t)mt0 * NN_TM, NN_TM * sizeof(float4), &mbar);
         }
 
-        // ---- compute: 8 scene points x 512 model points per thread --------------------------------
-        const float4* X4 = reinterpret_cast<const float4*>(buf);
-        const float4* Y4 = reinterpret_cast<const float4*>(buf + SOA_PLANE);
-        const float4* Z4 = reinterpret_cast<const float4*>(buf + 2 * SOA_PLANE);
-        const float4* W4 = reinterpret_cast<const float4*>(buf + 3 * SOA_PLANE);
-#pragma unroll 1
-        for (int c = 0; c < NN_TM / NN_G; ++c) {
-            float tmin[NN_R];
+        // CTA-local origin: the middle point of the (Morton-sorted) scene tile.
+        const float cx = phx[pbase + NN_TILE / 2], cy = phy[pbase + NN_TILE / 2], cz = phz[pbase + NN_TILE / 2];
+
+        float2 ax[NN_R], ay[NN_R], az[NN_R];
+        float best[NN_R], runner[NN_R];
+        uint32_t bchunk[NN_R];
 #pragma unroll
-            for (int r = 0; r < NN_R; ++r) tmin[r] = __int_as_float(0x7f800000);
+        for (int r = 0; r < NN_R; ++r) {
+            const int j = pbase + r * NN_THREADS + tid;
+            const float x = -2.0f * __fsub_rn(phx[j], cx);
+            const float y = -2.0f * __fsub_rn(phy[j], cy);
+            const float z = -2.0f * __fsub_rn(phz[j], cz);
+            ax[r] = make_float2(x, x);
+            ay[r] = make_float2(y, y);
+            az[r] = make_float2(z, z);
+            best[r] = __int_as_float(0x7f800000);
+            runner[r] = __int_as_float(0x7f800000);
+            bchunk[r] = 0u;
+        }
+
+        for (int mt = mt0; mt < mt1; ++mt) {
+            float* buf = soa + ((mt - mt0) & 1) * SOA_BUF;
+            // ---- stage: raw float4 (TMA) -> CTA-local SoA planes --------------------------------------
+            mbar_wait(&mbar, parity);
+            parity ^= 1u;
+#pragma unroll
+            for (int k = 0; k < NN_TM / NN_THREADS; ++k) {
+                const int i = k * NN_THREADS + tid;
+                const float4 v = raw[i];
+                const float x = __fsub_rn(v.x, cx), y = __fsub_rn(v.y, cy), z = __fsub_rn(v.z, cz);
+                buf[i] = x;
+                buf[SOA_PLANE + i] = y;
+                buf[2 * SOA_PLANE + i] = z;
+                buf[3 * SOA_PLANE + i] = __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x)));
+            }
+            __syncthreads();   // planes visible; everyone is done with `raw` and with the other buffer
+            if (tid == 0 && mt + 1 < mt1) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(&mbar, NN_TM * sizeof(float4));
+                bulk_g2s(raw, mhat + (size_t)(mt + 1) * NN_TM, NN_TM * sizeof(float4), &mbar);
+            }
+
+            // ---- compute: 8 scene points x (up to) 512 model points per thread --------------------------
+            const float4* X4 = reinterpret_cast<const float4*>(buf);
+            const float4* Y4 = reinterpret_cast<const float4*>(buf + SOA_PLANE);
+            const float4* Z4 = reinterpret_cast<const float4*>(buf + 2 * SOA_PLANE);
+            const float4* W4 = reinterpret_cast<const float4*>(buf + 3 * SOA_PLANE);
+            const int cb = max(c_lo - mt * CPM, 0), ce = min(c_hi - mt * CPM, CPM);   // the segment's share of this tile
+#pragma unroll 1
+            for (int c = cb; c < ce; ++c) {
+                float tmin[NN_R];
+#pragma unroll
+                for (int r = 0; r < NN_R; ++r) tmin[r] = __int_as_float(0x7f800000);
 #pragma unroll 2
-            for (int q = 0; q < NN_G / 4; ++q) {
-                const int o = c * (NN_G / 4) + q;
-                const float4 X = X4[o], Y = Y4[o], Z = Z4[o], W = W4[o];
-                const float2 x01 = make_float2(X.x, X.y), x23 = make_float2(X.z, X.w);
-                const float2 y01 = make_float2(Y.x, Y.y), y23 = make_float2(Y.z, Y.w);
-                const float2 z01 = make_float2(Z.x, Z.y), z23 = make_float2(Z.z, Z.w);
-                const float2 w01 = make_float2(W.x, W.y), w23 = make_float2(W.z, W.w);
+                for (int q = 0; q < NN_G / 4; ++q) {
+                    const int o = c * (NN_G / 4) + q;
+                    const float4 X = X4[o], Y = Y4[o], Z = Z4[o], W = W4[o];
+                    const float2 x01 = make_float2(X.x, X.y), x23 = make_float2(X.z, X.w);
+                    const float2 y01 = make_float2(Y.x, Y.y), y23 = make_float2(Y.z, Y.w);
+                    const float2 z01 = make_float2(Z.x, Z.y), z23 = make_float2(Z.z, Z.w);
+                    const float2 w01 = make_float2(W.x, W.y), w23 = make_float2(W.z, W.w);
+#pragma unroll
+                    for (int r = 0; r < NN_R; ++r) {
+                        float2 t01 = __ffma2_rn(az[r], z01, w01);
+                        float2 t23 = __ffma2_rn(az[r], z23, w23);
+                        t01 = __ffma2_rn(ay[r], y01, t01);
+                        t23 = __ffma2_rn(ay[r], y23, t23);
+                        t01 = __ffma2_rn(ax[r], x01, t01);
+                        t23 = __ffma2_rn(ax[r], x23, t23);
+                        tmin[r] = min3(tmin[r], t01.x, t01.y);
+                        tmin[r] = min3(tmin[r], t23.x, t23.y);
+                    }
+                }
+                const uint32_t cid = (uint32_t)mt * CPM + (uint32_t)c;
 #pragma unroll
                 for (int r = 0; r < NN_R; ++r) {
-                    float2 t01 = __ffma2_rn(az[r], z01, w01);
-                    float2 t23 = __ffma2_rn(az[r], z23, w23);
-                    t01 = __ffma2_rn(ay[r], y01, t01);
-                    t23 = __ffma2_rn(ay[r], y23, t23);
-                    t01 = __ffma2_rn(ax[r], x01, t01);
-                    t23 = __ffma2_rn(ax[r], x23, t23);
-                    tmin[r] = min3(tmin[r], t01.x, t01.y);
-                    tmin[r] = min3(tmin[r], t23.x, t23.y);
+                    const float tm = tmin[r];
+                    const bool lt = tm < best[r];
+                    runner[r] = fminf(runner[r], fmaxf(best[r], tm));
+                    bchunk[r] = lt ? cid : bchunk[r];
+                    best[r] = fminf(best[r], tm);
                 }
             }
-            const uint32_t cid = (uint32_t)mt * (NN_TM / NN_G) + (uint32_t)c;
-#pragma unroll
-            for (int r = 0; r < NN_R; ++r) {
-                const float tm = tmin[r];
-                const bool lt = tm < best[r];
-                runner[r] = fminf(runner[r], fmaxf(best[r], tm));
-                bchunk[r] = lt ? cid : bchunk[r];
-                best[r] = fminf(best[r], tm);
-            }
         }
-    }
 
-    const size_t obase = (size_t)split * np_pad + pbase;
+        const size_t obase = (size_t)slot * np_pad + pbase;
 #pragma unroll
-    for (int r = 0; r < NN_R; ++r) {
-        const size_t j = obase + r * NN_THREADS + tid;
-        out_best[j] = best[r];
-        out_runner[j] = runner[r];
-        out_chunk[j] = bchunk[r];
+        for (int r = 0; r < NN_R; ++r) {
+            const size_t j = obase + r * NN_THREADS + tid;
+            out_best[j] = best[r];
+            out_runner[j] = runner[r];
+            out_chunk[j] = bchunk[r];
+        }
+        remaining -= c_hi - c_lo;
+        c_lo = 0;
+        ++tile;
+        __syncthreads();       // the shared buffers are reused by the next segment
     }
 }
 
@@ -267,7 +299,8 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
                  const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
                  const double* __restrict__ p64x, const double* __restrict__ p64y, const double* __restrict__ p64z,
                  const float* __restrict__ phx, const float* __restrict__ phy, const float* __restrict__ phz, int np,
-                 int np_pad, int n_splits, const float* __restrict__ part_best, const float* __restrict__ part_runner,
+                 int np_pad, int n_tiles, int cpt, int n_cta, const float* __restrict__ part_best,
+                 const float* __restrict__ part_runner,
                  const uint32_t* __restrict__ part_chunk, int32_t* __restrict__ idx, int32_t* __restrict__ amb_list,
                  float* __restrict__ amb_thr, int* __restrict__ ctl, int honor_done)
 {
@@ -288,10 +321,12 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         const float hx = phx[j], hy = phy[j], hz = phz[j];
         const float cx = phx[cj], cy = phy[cj], cz = phz[cj];
         const double px = p64x[j], py = p64y[j], pz = p64z[j];
-        // ---- merge the model splits (RF lanes stride over the splits) ------------------------------
+        // ---- merge the partial results of this scene tile (RF lanes stride over its slots) -----------
+        const long long T = (long long)n_tiles * cpt, x0 = (long long)(j / NN_TILE) * cpt;
+        const int n_slots = cta_of_unit(x0 + cpt - 1, T, n_cta) - cta_of_unit(x0, T, n_cta) + 1;
         float b = INF, rn = INF;
         uint32_t ch = 0;
-        for (int s = sub; s < n_splits; s += RF) {
+        for (int s = sub; s < n_slots; s += RF) {
             const size_t o = (size_t)s * np_pad + j;
             const float sb = part_best[o], sr = part_runner[o];
             const uint32_t sc = part_chunk[o];
@@ -508,12 +543,9 @@ void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
         cudaFuncSetAttribute(nn_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FILTER_SMEM);
         attr_set = true;
     }
-    const int n_tiles = (int)(s.np_pad / NN_TILE);
-    const int nm_tiles = (int)(m.nm_pad / NN_TM);
-    const int grid = n_tiles * sc.n_splits;
-    nn_filter_kernel<<<grid, NN_THREADS, FILTER_SMEM, st>>>(m.mhat, s.phx, s.phy, s.phz, (int)s.np_pad, sc.n_splits,
-                                                            sc.tiles_per_split, nm_tiles, sc.best, sc.runner,
-                                                            sc.chunk, ctl, honor_done);
+    nn_filter_kernel<<<sc.n_cta, NN_THREADS, FILTER_SMEM, st>>>(m.mhat, s.phx, s.phy, s.phz, (int)s.np_pad,
+                                                                (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.best,
+                                                                sc.runner, sc.chunk, ctl, honor_done);
 }
 
 void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
@@ -525,7 +557,8 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
     if (grid < 1) grid = 1;
     nn_refine_kernel<<<grid, REFINE_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.mhat, (int)m.nm, m.geo, s.p64x, s.p64y,
                                                       s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)s.np_pad,
-                                                      sc.n_splits, sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list,
+                                                      (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.n_cta,
+                                                      sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list,
                                                       sc.amb_thr, ctl, honor_done);
 }
 

@@ -43,11 +43,11 @@ if __name__ == "__main__":
     closest_timing("cow", cow_r, cow_1); loop_timing("cow", cow_r, cow_1)
     h_r, h_1 = load("horse_ref"), load("horse_tr1")
     closest_timing("horse", h_r, h_1); loop_timing("horse_tr1", h_r, h_1)
-    for s in os.environ.get("QB_SPLITS", "").split(","):
+    for s in os.environ.get("QB_CTAS", "").split(","):
         if s:
-            os.environ["ICP_NN_SPLITS"] = s
-            closest_timing(f"horse splits={s}", h_r, h_1)
-    os.environ.pop("ICP_NN_SPLITS", None)
+            os.environ["ICP_NN_CTAS"] = s
+            closest_timing(f"horse ctas={s}", h_r, h_1)
+    os.environ.pop("ICP_NN_CTAS", None)
     for lg in (18, 20):
         m, p, _ = synthetic_pair(1 << lg, seed=lg)
         closest_timing(f"synthetic 2^{lg}", m, p, reps=3)
