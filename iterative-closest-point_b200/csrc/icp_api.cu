@@ -137,11 +137,12 @@ void choose_splits(icp_ctx* c)
     const long long cpt = c->m.nm_pad / NN_G;
     const long long total = n_tiles * cpt;
     const long long wave = (long long)c->sm_count * 4;
-    long long waves = (total + 1024 * wave - 1) / (1024 * wave);
+    const long long per_cta = 65536 / NN_G;             // ~64 K model points x 1 scene tile per CTA and wave
+    long long waves = (total + per_cta * wave - 1) / (per_cta * wave);
     if (waves < 1) waves = 1;
     long long n_cta = wave * waves;
     if (c->forced_ctas > 0) n_cta = c->forced_ctas;
-    if (n_cta > total / 8) n_cta = total / 8;
+    if (n_cta > total / (NN_TM / NN_G)) n_cta = total / (NN_TM / NN_G);
     if (n_cta < 1) n_cta = 1;
     c->sc.n_cta = (int)n_cta;
     c->sc.n_splits = (int)((n_cta + n_tiles - 1) / n_tiles + 1);

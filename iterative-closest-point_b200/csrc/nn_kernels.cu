@@ -406,7 +406,7 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
 constexpr int EXACT_THREADS = 256;
 constexpr int EX_P = 4;          // queued points per batch
 constexpr int EX_U = 4;          // model points in flight per thread
-constexpr int EX_MIN_SEG = 4096; // model points per segment at least
+constexpr int EX_MIN_SEG = 4096; // model points per segment at least (1024 was measured slower: more tickets and merges)
 
 __global__ void __launch_bounds__(EXACT_THREADS)
 nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
