@@ -507,7 +507,7 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
     block_sum<17>(acc, red);
     if (threadIdx.x == 0)
 #pragma unroll
-        for (int i = 0; i < 17; ++i) partials[(size_t)blockIdx.x * 17 + i] = acc[i];
+        for (int i = 0; i < 17; ++i) partials[(size_t)i * nb + blockIdx.x] = acc[i];   // [17][nb]: coalesced re-reads
     TRACE(2);
     grid.sync();
     TRACE(3);
@@ -519,7 +519,7 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
         for (int i = 0; i < 17; ++i) tot[i] = 0.0;
         for (int b = threadIdx.x; b < nb; b += RED_THREADS)
 #pragma unroll
-            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)b * 17 + i]);
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)i * nb + b]);
         block_sum<17>(tot, red);
         if (threadIdx.x == 0) {
             mom_s[0] = (double)np;

@@ -539,6 +539,21 @@ int oracle_horn_quaternion(const double N[16], int eig_mode, double q[4], double
 }
 
 // src/cpu.cc:138-152: R = (q_bar^T q_caps)[1:4,1:4], row-major.
+// General real eigen-decomposition of a 4x4 matrix with real spectrum (Horn's N is symmetric): eigenvalues in the
+// order of the quasi-triangular form's diagonal, eigenvectors (unit 2-norm) as the columns of the row-major vec.
+// Used by oracle/eigen_shim/Eigen/Eigenvalues (the stand-in EigenSolver behind oracle/_ref).
+int oracle_general_eig4(const double A[16], double wr[4], double wi[4], double vec[16])
+{
+    GeneralEig4 g;
+    if (!g.compute(A)) return -1;
+    for (int i = 0; i < 4; ++i) {
+        wr[i] = g.wr[i];
+        wi[i] = 0.0;
+        for (int j = 0; j < 4; ++j) vec[i * 4 + j] = g.vec[i][j];
+    }
+    return 0;
+}
+
 void oracle_quat_to_rot(const double q[4], double R[9])
 {
     const double q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];

@@ -87,3 +87,55 @@ def test_shard_range_partitions():
             assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
             sizes = [b - a for a, b in edges]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_peer_mailbox_protocol_model():
+    """Host model of peer_allreduce (csrc/align_kernels.cu): every rank posts its values into slot [q & 1][rank]
+    of EVERY rank's mailbox, publishes q in the slot's flag, waits for the flags of all ranks in its own mailbox,
+    then adds the slots in rank order.  Threads with random stalls stand in for GPUs; the model checks what the
+    kernel relies on: sums are right and bit-identical on all ranks over hundreds of back-to-back exchanges with
+    only TWO buffers per slot (a rank can be at most one exchange ahead of the slowest peer) and flags that
+    are never reset (monotonic sequence numbers)."""
+    import random
+    import threading
+    import time
+
+    world, rounds, n = 4, 300, 18
+    data = np.zeros((world, 2, world, n))          # data[owner][parity][source]
+    flag = np.zeros((world, 2, world), dtype=np.int64)
+    results = [[None] * rounds for _ in range(world)]
+    rng = np.random.default_rng(0)
+    contrib = rng.standard_normal((rounds, world, n))
+    errors = []
+
+    def rank_fn(r):
+        rnd = random.Random(r)
+        for i in range(rounds):
+            q = i + 1
+            par = q & 1
+            if rnd.random() < 0.2:
+                time.sleep(rnd.random() * 2e-3)     # a slow rank
+            for dst in range(world):                # post, then publish
+                data[dst, par, r, :] = contrib[i, r]
+                flag[dst, par, r] = q
+            t0 = time.time()
+            while not all(flag[r, par, src] == q for src in range(world)):
+                if time.time() - t0 > 20:
+                    errors.append((r, q, "timeout"))
+                    return
+                time.sleep(0)
+            acc = np.zeros(n)
+            for src in range(world):                # rank order: identical everywhere
+                acc = acc + data[r, par, src]
+            results[r][i] = acc
+
+    th = [threading.Thread(target=rank_fn, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errors, errors
+    for i in range(rounds):
+        want = np.zeros(n)
+        for src in range(world):
+            want = want + contrib[i, src]
+        for r in range(world):
+            assert np.array_equal(results[r][i], want), (r, i)
