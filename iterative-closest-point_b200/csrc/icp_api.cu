@@ -108,7 +108,9 @@ struct icp_ctx {
     int align_blocks_max = 148;
     PeerMailbox* d_mailbox = nullptr;
     PeerComm peer;
-    bool peer_ready = false, force_nccl = false, align_fused = false;
+    bool peer_ready = false, force_nccl = false;
+    int align_mode = 0;                    // 0 auto, 1 fused, 2 split (ICP_ALIGN)
+    bool is_lane = false;                  // a context of icp_batch_run: shares the GPU with other lanes
     unsigned long long seq = 0;            // exchanges issued so far (identical on every rank)
     unsigned long long* d_trace = nullptr; // ICP_PROFILE=1: phase time stamps of the last fused alignment kernel
     bool profile = false;                  // ICP_PROFILE=1: events between all kernels of icp_run (adds ~us per iteration)
@@ -187,11 +189,12 @@ void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1, cudaEve
     c->stats.kernels_launched += 3;
 }
 
-// Alignment step (K2 -> K3 -> K4) of one iteration.  Two device-only forms, both carrying the multi-GPU
+// Alignment step (K2 -> K3 -> K4) of one iteration.  Two device-only forms, both able to carry the multi-GPU
 // exchange INSIDE the kernels once peer mailboxes are attached:
-//   split (default)  moments_kernel (last block: reduce, exchange, Horn solve) + transform_kernel (last block:
-//                    reduce, exchange, close the iteration): 2 launches, no grid barrier
-//   fused            ICP_ALIGN=fused: one cooperative launch with a grid barrier (align_fused_kernel)
+//   fused  one cooperative launch with a grid barrier (align_fused_kernel)
+//   split  moments_kernel (last block: reduce, exchange, Horn solve) + transform_kernel (last block: reduce,
+//          exchange, close the iteration): 2 launches, no grid barrier, no co-residency requirement
+// ICP_ALIGN=fused|split forces one; the default picks per context (see align_step).
 // A communicator without mailboxes (or ICP_COMM=nccl) takes the NCCL path: separate kernels + ncclAllReduce.
 bool nccl_path(const icp_ctx* c) { return c->comm && (!c->peer_ready || c->force_nccl); }
 
@@ -208,7 +211,11 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
 {
     const PeerComm* peers = (c->comm && c->peer_ready) ? &c->peer : nullptr;
     int launched;
-    if (c->align_fused) {
+    // auto: the cooperative kernel where it was measured faster (one GPU, nothing else on it: 11.17 vs 11.27 ms per
+    // horse loop), the split pair with peers (its second grid barrier costs more than a launch: 11.65 vs 11.61 ms
+    // at N = 2) and in batch lanes (no co-residency requirement between concurrent contexts).
+    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->is_lane);
+    if (fused) {
         const int e = launch_align_fused(c->m, c->s, c->d_partials, fused_blocks(c), c->d_mom, c->d_xf, c->d_err_sum,
                                          c->d_ctl, honor_done, in_place, finish, n_global, threshold, c->d_err_hist, peers,
                                          c->seq + 1, c->profile ? c->d_trace : nullptr, c->st);
@@ -288,7 +295,7 @@ int icp_create(icp_ctx** out, int device)
     CK(cudaMemset(c->d_trace, 0, 16 * sizeof(unsigned long long)));
     c->align_blocks_max = align_fused_max_blocks(c->sm_count);
     if (const char* e = getenv("ICP_COMM")) c->force_nccl = !strcmp(e, "nccl");
-    if (const char* e = getenv("ICP_ALIGN")) c->align_fused = !strcmp(e, "fused");
+    if (const char* e = getenv("ICP_ALIGN")) c->align_mode = !strcmp(e, "fused") ? 1 : (!strcmp(e, "split") ? 2 : 0);
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
     if (const char* e = getenv("ICP_NN_CTAS")) c->forced_ctas = atoi(e);
@@ -837,6 +844,7 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     auto worker = [&]() {
         icp_ctx* c = lane_pool_take(device);       // contexts survive between calls: no per-call cudaMalloc storm
         int r = c ? ICP_OK : icp_create(&c, device);
+        if (c) c->is_lane = true;
         std::vector<double> hist((size_t)(max_iter > 0 ? max_iter : 1));
         while (!r && status.load() == ICP_OK) {
             const int64_t k = next.fetch_add(1);

@@ -14,6 +14,8 @@ iterative-closest-point_b200/bin/bench /tmp/cl/cow_ref.txt /tmp/cl/cow_tr1.txt >
 iterative-closest-point_b200/bin/bench /tmp/cl/horse_ref.txt /tmp/cl/horse_tr1.txt > gpurun_out/cppbench_horse.txt 2>/dev/null
 timeout 600 python tools/prof_step.py horse 3 > gpurun_out/prof_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_horse.csv python tools/prof_step.py horse 3 > gpurun_out/ncu_launch.log 2>&1
+# the launch list of the bench command itself (timed region only: skip set-up + 3 warm-up steps)
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 470 -c 330 --csv --log-file gpurun_out/launches_bench.csv python bench.py --steps 2 --warmup 3 > gpurun_out/ncu_launch_bench.log 2>&1
 if [ -n "$1" ]; then
   timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$1" -s 2 -c 1 -o gpurun_out/full_$1 python tools/prof_step.py horse 3 > gpurun_out/ncu_full.log 2>&1
 fi
