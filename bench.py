@@ -146,6 +146,30 @@ def cpu_port_throughput(m, p, iters, threads=0):
     return r["iters"] * len(m) * len(p) / dt, r["iters"], dt, (threads or O.num_threads())
 
 
+def ref_source_throughput(m, p, max_pairs=2.0e7):
+    """Extra context for cpu_baseline: the reference's OWN src/cpu.cc (oracle/_ref, compiled against the Eigen stand-in;
+    single-threaded like the reference) on a small sample of CPU::closest_matrix.  Not the timed baseline — a
+    stand-in Eigen says little about real Eigen's speed — but it is the reference's source text running."""
+    so = os.path.join(ROOT, "oracle", "_ref", "libref_cpu.so")
+    if not os.path.exists(so):
+        return None
+    import ctypes as C
+    try:
+        L = C.CDLL(so)
+        dp = C.POINTER(C.c_double)
+        L.ref_closest_matrix.argtypes = [C.c_long, C.c_long, dp, dp, dp]
+        n_scene = int(max(1, min(len(p), max_pairs // len(m))))
+        ps = np.ascontiguousarray(p[:n_scene])
+        Y = np.empty_like(ps)
+        t0 = time.perf_counter()
+        L.ref_closest_matrix(len(ps), len(m), ps.ctypes.data_as(dp), m.ctypes.data_as(dp), Y.ctypes.data_as(dp))
+        dt = time.perf_counter() - t0
+        return {"value": len(ps) * len(m) / dt, "unit": "evals/s", "cores": 1, "kind": "reference source (src/cpu.cc) + Eigen stand-in",
+                "sample": f"CPU::closest_matrix, {len(ps)} scene x {len(m)} model points"}
+    except Exception as e:      # never let the extra line break the bench
+        return {"error": str(e)}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU path (oracle port; Eigen is absent so cpu.cc cannot be
     compiled) on the host cores, all threads, on a bounded sample of the same workload."""
@@ -169,7 +193,8 @@ def run_reference(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "reference clouds",
             "icp_iterations_per_sec": float(np.mean([it / dt for _, it, dt in vals])),
             "config": {"workload": args.workload, "description": desc},
-            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample,
+                             "reference_source": ref_source_throughput(m, p)},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -287,7 +312,8 @@ def run_ours(args, rank, world, local_rank):
         pc = p if len(m) * len(p) < 1e11 else p[:4096]
         cv, cit, cdt, cores = cpu_port_throughput(m, pc, cpu_iters, threads=host_threads())
         cpu = {"value": cv, "unit": "evals/s", "cores": cores, "kind": "port",
-               "sample": f"{cit} ICP iteration(s), {len(pc)} scene x {len(m)} model points, oracle x*x+sqrt form"}
+               "sample": f"{cit} ICP iteration(s), {len(pc)} scene x {len(m)} model points, oracle x*x+sqrt form",
+               "reference_source": ref_source_throughput(m, p)}
     line = {
         "metric": "nn_distance_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,

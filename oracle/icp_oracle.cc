@@ -11,8 +11,10 @@
 //
 // Parity pinning: the reference holds exactly one known answer for this path — `./icp cow_ref.txt
 // cow_tr1.txt 10` runs 7 iterations (benchmark/callgrind.out.76685:5,28306-28308).  tests/ assert
-// it.  Everything else (indices, s/R/t, err, other iteration counts) is defined by this restatement:
-// "parity unpinned" beyond that one datum.
+// it.  Beyond that datum this restatement is checked against the reference's OWN src/cpu.cc, compiled in
+// place against an Eigen stand-in (oracle/_ref, oracle/eigen_shim, tests/test_ref_cpu.py): indices, Horn
+// solve, residuals and the 7-iteration loop agree.  Still "parity unpinned": Eigen's own numerics
+// (EigenSolver's eigenvalue order, reduction order of long sums), which no stand-in can reproduce.
 //
 // Modes
 //   nn_mode 0  literal : sqrt(pow(dx,2)+pow(dy,2)+pow(dz,2)), libm pow/sqrt   (src/cpu.cc:17-19)
