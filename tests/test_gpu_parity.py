@@ -177,6 +177,28 @@ def test_closest_large_scale_property(icp):
     ctx.close()
 
 
+def test_closest_full_size_property_4m(icp):
+    # BASELINE's largest single cloud (2^22 points, 1.76e13 pairs): the scene is a rigidly moved copy of the
+    # model in a different order, with a shift far below the point spacing, so the exact answer is the inverse
+    # permutation; then one alignment step must recover the motion (s = 1, R, t) to 1e-9.
+    rng = np.random.default_rng(22)
+    n = 1 << 22
+    m = rng.uniform(-1, 1, (n, 3))
+    perm = rng.permutation(n)
+    a = 1e-7
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1.0]])
+    t = np.array([2e-7, -1e-7, 3e-7])
+    ctx = icp.Context(0)
+    ctx.set_model(m)
+    ctx.set_scene((m @ R.T + t)[perm])
+    idx, _ = ctx.closest(want_Y=False)
+    assert np.array_equal(idx, perm.astype(np.int32))
+    fa = ctx.find_alignment()
+    assert abs(fa["s"] - 1.0) < 1e-9 and np.abs(fa["R"] - R.T).max() < 1e-9 and np.abs(fa["t"] + R.T @ t).max() < 1e-9
+    assert fa["err"] < 1e-18 * n
+    ctx.close()
+
+
 # ---- K2-K4 operators ------------------------------------------------------------------------------
 
 def test_find_alignment_and_err_compute(icp, clouds):
