@@ -63,10 +63,14 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
     return t;
 }
 
-__device__ void peer_allreduce(const PeerComm& pc, unsigned long long seq, const double* vals, int n, double* out,
-                               double* stage, int* ctl)
+__device__ void peer_allreduce(const PeerComm& pc, const double* vals, int n, double* out, double* stage, int* ctl)
 {
     const int lane = threadIdx.x;                    // caller: threadIdx.x < 32
+    // The exchange number lives in this rank's own mailbox and advances only when an exchange really happens, so
+    // the ranks stay in step however many (no-op) launches each host has queued after convergence.
+    PeerMailbox* self = pc.box[pc.rank];
+    const unsigned long long seq = ld_acquire_sys(&self->seq_local) + 1ull;
+    __syncwarp();
     const int par = (int)(seq & 1ull);
     if (lane < pc.world) {
         PeerMailbox* dst = pc.box[lane];             // post to rank `lane` (own mailbox included)
@@ -87,6 +91,7 @@ __device__ void peer_allreduce(const PeerComm& pc, unsigned long long seq, const
         for (int r = 0; r < pc.world; ++r) acc += stage[r * PEER_SLOT + lane];     // rank order: identical everywhere
         out[lane] = acc;
     }
+    if (lane == 0) { self->seq_local = seq; __threadfence(); }
     __syncwarp();
 }
 
@@ -97,7 +102,7 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
                const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
                const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
                double* __restrict__ mom, int* __restrict__ ctl, int honor_done, double* __restrict__ xf_fused,
-               PeerComm pc, unsigned long long seq)
+               PeerComm pc)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     __shared__ double red[17 * (RED_THREADS / 32)];
@@ -147,7 +152,7 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
         __syncthreads();
         if (threadIdx.x < 32) {
             // multi-GPU: the 18 sums of all ranks meet here, inside the kernel (peer mailboxes over NVLink)
-            if (pc.world > 0) peer_allreduce(pc, seq, mom_s, MOM_N, mom_s, stage, ctl);
+            if (pc.world > 0) peer_allreduce(pc, mom_s, MOM_N, mom_s, stage, ctl);
             if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
             __syncwarp();
             if (threadIdx.x == 0 && xf_fused) horn_solve(geo, mom_s, xf_fused);   // K3 rides on K2's last block
@@ -391,8 +396,7 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
                  double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
                  const int32_t* __restrict__ idx, int np, int np_pad, const double* __restrict__ xf, int in_place,
                  double* __restrict__ partials, double* __restrict__ err_sum, int* __restrict__ ctl, int honor_done,
-                 int finish, double n_global, double threshold, double* __restrict__ err_hist, PeerComm pc,
-                 unsigned long long seq)
+                 int finish, double n_global, double threshold, double* __restrict__ err_hist, PeerComm pc)
 {
     if (honor_done && ctl[CTL_DONE]) return;
     __shared__ double red[RED_THREADS / 32];
@@ -424,7 +428,7 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         if (threadIdx.x == 0) tot_s[0] = tot[0];
         __syncthreads();
         if (threadIdx.x < 32) {
-            if (pc.world > 0) peer_allreduce(pc, seq, tot_s, 1, tot_s, stage, ctl);
+            if (pc.world > 0) peer_allreduce(pc, tot_s, 1, tot_s, stage, ctl);
             if (threadIdx.x == 0) {
                 const double total = tot_s[0];
                 err_sum[0] = total;
@@ -470,8 +474,7 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
                    const int32_t* __restrict__ idx, int np, int np_pad, double* __restrict__ partials,
                    double* __restrict__ mom, double* __restrict__ xf, double* __restrict__ err_sum,
                    int* __restrict__ ctl, int honor_done, int in_place, int finish, double n_global, double threshold,
-                   double* __restrict__ err_hist, PeerComm pc, unsigned long long seq,
-                   unsigned long long* __restrict__ trace)
+                   double* __restrict__ err_hist, PeerComm pc, unsigned long long* __restrict__ trace)
 {
     if (honor_done && ctl[CTL_DONE]) return;                 // uniform over the grid: nobody reaches a barrier
     // diagnostic (ICP_PROFILE=1): block 0 stamps %globaltimer at its phase boundaries
@@ -531,7 +534,7 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
     if (pc.world > 0) {
         if (blockIdx.x == 0) {
             if (threadIdx.x < 32) {
-                peer_allreduce(pc, seq, mom_s, MOM_N, mom_s, stage, ctl);
+                peer_allreduce(pc, mom_s, MOM_N, mom_s, stage, ctl);
                 if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
                 __threadfence();
             }
@@ -578,7 +581,7 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
         if (threadIdx.x == 0) mom_s[0] = tot[0];
         __syncthreads();
         if (threadIdx.x < 32) {
-            if (pc.world > 0) peer_allreduce(pc, seq + 1, mom_s, 1, mom_s, stage, ctl);
+            if (pc.world > 0) peer_allreduce(pc, mom_s, 1, mom_s, stage, ctl);
             if (threadIdx.x == 0) {
                 const double total = mom_s[0];
                 err_sum[0] = total;
@@ -819,12 +822,12 @@ int reduce_blocks_for(int64_t n, int sm_count)
 }
 
 void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
-                    int honor_done, double* xf_fused, cudaStream_t st, const PeerComm* peer, unsigned long long seq)
+                    int honor_done, double* xf_fused, cudaStream_t st, const PeerComm* peer)
 {
     PeerComm pc;
     if (peer) pc = *peer;
     moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
-                                                     (int)s.np, partials, mom, ctl, honor_done, xf_fused, pc, seq);
+                                                     (int)s.np, partials, mom, ctl, honor_done, xf_fused, pc);
 }
 
 void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st)
@@ -834,14 +837,14 @@ void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* c
 
 void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, int in_place, double* partials,
                       int n_blocks, double* err_sum, int* ctl, int honor_done, int finish, double n_global,
-                      double threshold, double* err_hist, cudaStream_t st, const PeerComm* peer, unsigned long long seq)
+                      double threshold, double* err_hist, cudaStream_t st, const PeerComm* peer)
 {
     PeerComm pc;
     if (peer) pc = *peer;
     transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
                                                        s.phy, s.phz, s.idx, (int)s.np, (int)s.np_pad, xf, in_place,
                                                        partials, err_sum, ctl, honor_done, finish, n_global,
-                                                       threshold, err_hist, pc, seq);
+                                                       threshold, err_hist, pc);
 }
 
 int align_fused_max_blocks(int sm_count)
@@ -855,8 +858,8 @@ int align_fused_max_blocks(int sm_count)
 
 int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, double* xf,
                        double* err_sum, int* ctl, int honor_done, int in_place, int finish, double n_global,
-                       double threshold, double* err_hist, const PeerComm* peer, unsigned long long seq,
-                       unsigned long long* trace, cudaStream_t st)
+                       double threshold, double* err_hist, const PeerComm* peer, unsigned long long* trace,
+                       cudaStream_t st)
 {
     PeerComm pc;
     if (peer) pc = *peer;
@@ -866,7 +869,7 @@ int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, i
     float *f0 = s.phx, *f1 = s.phy, *f2 = s.phz;
     const int32_t* ix = s.idx;
     void* args[] = {&a0, &a1, &a2, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum,
-                    &ctl, &honor_done, &in_place, &finish, &n_global, &threshold, &err_hist, &pc, &seq, &trace};
+                    &ctl, &honor_done, &in_place, &finish, &n_global, &threshold, &err_hist, &pc, &trace};
     return (int)cudaLaunchCooperativeKernel((const void*)align_fused_kernel, dim3(n_blocks), dim3(RED_THREADS), args, 0, st);
 }
 

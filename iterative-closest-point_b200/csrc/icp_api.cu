@@ -83,6 +83,7 @@ NcclApi g_nccl;
 
 }  // namespace
 
+
 struct icp_ctx {
     int device = 0, sm_count = 148;
     cudaStream_t st = nullptr;
@@ -111,8 +112,12 @@ struct icp_ctx {
     bool peer_ready = false, force_nccl = false;
     int align_mode = 0;                    // 0 auto, 1 fused, 2 split (ICP_ALIGN)
     bool is_lane = false;                  // a context of icp_batch_run: shares the GPU with other lanes
-    unsigned long long seq = 0;            // exchanges issued so far (identical on every rank)
     unsigned long long* d_trace = nullptr; // ICP_PROFILE=1: phase time stamps of the last fused alignment kernel
+    // early stop of the enqueue loop: the done flag of every chunk of iterations is copied to pinned memory
+    int* h_progress = nullptr;             // mapped pinned word the loop's closing kernel writes: (iterations closed << 1) | converged
+    int* d_progress = nullptr;             // its device address
+    int* progress_arg = nullptr;           // what nn_pass hands to the filter kernel (set by icp_run only)
+    int lookahead = 3;                     // ICP_LOOKAHEAD: iterations icp_run keeps enqueued ahead of the device (0 = all at once)
     bool profile = false;                  // ICP_PROFILE=1: events between all kernels of icp_run (adds ~us per iteration)
 };
 
@@ -180,7 +185,7 @@ void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1, cudaEve
              cudaEvent_t e3 = nullptr)
 {
     if (e0) cudaEventRecord(e0, c->st);
-    launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
+    launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st, c->progress_arg);
     if (e1) cudaEventRecord(e1, c->st);
     launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
     if (e2) cudaEventRecord(e2, c->st);
@@ -205,7 +210,33 @@ int fused_blocks(const icp_ctx* c)
     return b < 1 ? 1 : (int)b;
 }
 
-// Enqueues one alignment step (not the NCCL path).  Consumes two exchange sequence numbers when peers are attached.
+// Spins on the loop's progress word until `need` iterations are closed; `enqueued` = iterations on the stream.
+// Returns 1 = stop enqueueing (converged, or the device stopped closing iterations), 0 = go on, < 0 = icp_status.
+int wait_progress(icp_ctx* c, int need, int enqueued)
+{
+    volatile int* p = c->h_progress;
+    for (unsigned spin = 1;; ++spin) {
+        const int v = *p;
+        if (v & 1) return 1;
+        if ((v >> 1) >= need) return 0;
+        if ((spin & 0x3ffu) == 0) {
+            const cudaError_t q = cudaStreamQuery(c->st);
+            if (q == cudaSuccess) {     // drained (the word lags one iteration: it is written when the next one starts)
+                int ctl[2];
+                CK(cudaMemcpy(ctl, c->d_ctl, sizeof(ctl), cudaMemcpyDeviceToHost));
+                // all enqueued iterations closed and not converged: the host was slow, go on; otherwise the loop
+                // converged or an error flag in ctl turned the kernels into no-ops
+                return (!ctl[CTL_DONE] && ctl[CTL_ITERS] == enqueued) ? 0 : 1;
+            }
+            if (q != cudaErrorNotReady) { g_err = std::string("icp_run: ") + cudaGetErrorString(q); return ICP_ERR_CUDA; }
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+}
+
+// Enqueues one alignment step (not the NCCL path).
 // Returns the number of kernels launched (> 0) or a negative icp_status.
 int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_global, double threshold)
 {
@@ -218,17 +249,15 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
     if (fused) {
         const int e = launch_align_fused(c->m, c->s, c->d_partials, fused_blocks(c), c->d_mom, c->d_xf, c->d_err_sum,
                                          c->d_ctl, honor_done, in_place, finish, n_global, threshold, c->d_err_hist, peers,
-                                         c->seq + 1, c->profile ? c->d_trace : nullptr, c->st);
+                                         c->profile ? c->d_trace : nullptr, c->st);
         if (e != 0) { g_err = std::string("align_fused launch: ") + cudaGetErrorString((cudaError_t)e); return ICP_ERR_CUDA; }
         launched = 1;
     } else {
-        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, honor_done, c->d_xf, c->st, peers,
-                       c->seq + 1);
+        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, honor_done, c->d_xf, c->st, peers);
         launch_transform(c->m, c->s, c->d_xf, in_place, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, honor_done,
-                         finish, n_global, threshold, c->d_err_hist, c->st, peers, c->seq + 2);
+                         finish, n_global, threshold, c->d_err_hist, c->st, peers);
         launched = 2;
     }
-    if (peers) c->seq += 2;
     return launched;
 }
 
@@ -297,6 +326,9 @@ int icp_create(icp_ctx** out, int device)
     if (const char* e = getenv("ICP_COMM")) c->force_nccl = !strcmp(e, "nccl");
     if (const char* e = getenv("ICP_ALIGN")) c->align_mode = !strcmp(e, "fused") ? 1 : (!strcmp(e, "split") ? 2 : 0);
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
+    if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
+    CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
     if (const char* e = getenv("ICP_NN_CTAS")) c->forced_ctas = atoi(e);
     if ((r = set_identity_xf(c))) { delete c; return r; }
@@ -313,6 +345,7 @@ void icp_destroy(icp_ctx* c)
     for (int r = 0; r < c->peer.world; ++r)
         if (c->peer_ready && r != c->peer.rank && c->peer.box[r]) cudaIpcCloseMemHandle(c->peer.box[r]);
     dfree(c->d_mailbox); dfree(c->d_trace);
+    if (c->h_progress) cudaFreeHost(c->h_progress);
     dfree(c->m.m64x); dfree(c->m.m64y); dfree(c->m.m64z); dfree(c->m.mhat); dfree(c->m.geo);
     dfree(c->s.p64x); dfree(c->s.p64y); dfree(c->s.p64z); dfree(c->s.q64x); dfree(c->s.q64y); dfree(c->s.q64z);
     dfree(c->s.phx); dfree(c->s.phy); dfree(c->s.phz); dfree(c->s.perm); dfree(c->s.idx);
@@ -599,7 +632,23 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     if ((r = reset_ctl(c))) return r;
     c->stats.kernels_launched = 0;
     CK(cudaEventRecord(c->ev0, c->st));
+    // The host runs ahead of the device and cannot know when the loop converges, so every kernel returns at entry
+    // once the device-side done flag is set; but even a no-op launch costs ~2.3 us, which for a small cloud that
+    // converges early (cow: 7 of 30 iterations) was 45 % of the whole call.  So the filter kernel
+    // stores, at entry, (iterations closed, converged) into one word of mapped pinned memory, and the host keeps at
+    // most `lookahead` iterations enqueued beyond the last one it saw closed: the device never waits for the host,
+    // nothing is added to the stream, and after convergence at most `lookahead` no-op iterations remain.  Not on the NCCL
+    // path: there every rank must issue the same collectives.  With peer mailboxes it is safe: the exchange
+    // number lives on the device (PeerMailbox::seq_local) and kernels after convergence do not exchange.
+    const int LA = (c->lookahead > 0 && !nccl_path(c)) ? (c->lookahead < 2 ? 2 : c->lookahead) : 0;   // >= 2: see nn_filter_kernel
+    *(volatile int*)c->h_progress = 0;
+    c->progress_arg = LA ? c->d_progress : nullptr;
     for (int it = 0; it < max_iter; ++it) {
+        if (LA && it >= LA) {
+            const int w = wait_progress(c, it + 1 - LA, it);
+            if (w < 0) return w;
+            if (w) break;
+        }
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
         nn_pass(c, 1, ev[0], ev[1], c->profile ? ev[2] : nullptr, c->profile ? ev[3] : nullptr);
         if (!nccl_path(c)) {
@@ -607,17 +656,18 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
             if (launched < 0) return launched;
             if (c->profile) cudaEventRecord(ev[4], c->st);
             c->stats.kernels_launched += launched;
-            continue;
+        } else {
+            launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, nullptr, c->st);
+            if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+            launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
+            launch_transform(c->m, c->s, c->d_xf, 1, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 1, 0, np_glob,
+                             threshold, c->d_err_hist, c->st);
+            if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+            launch_finish(c->d_err_sum, np_glob, threshold, c->d_err_hist, c->d_ctl, c->st);
+            c->stats.kernels_launched += 4;
         }
-        launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 1, nullptr, c->st);
-        if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
-        launch_solve(c->m, c->d_mom, c->d_xf, c->d_ctl, 1, c->st);
-        launch_transform(c->m, c->s, c->d_xf, 1, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 1, 0, np_glob,
-                         threshold, c->d_err_hist, c->st);
-        if ((r = allreduce(c, c->d_err_sum, 1))) return r;
-        launch_finish(c->d_err_sum, np_glob, threshold, c->d_err_hist, c->d_ctl, c->st);
-        c->stats.kernels_launched += 4;
     }
+    c->progress_arg = nullptr;
     CK(cudaEventRecord(c->ev1, c->st));
     CK(cudaGetLastError());
     int ctl[CTL_N];
@@ -945,7 +995,6 @@ int icp_comm_peer_attach(icp_ctx* c, const void* handles, int rank, int world)
     c->peer.rank = rank;
     c->peer.world = world;
     c->peer_ready = true;
-    c->seq = 0;
     return ICP_OK;
 }
 

@@ -33,8 +33,9 @@ enum { CTL_DONE = 0, CTL_ITERS = 1, CTL_AMB_COUNT = 2, CTL_TICKET_MOM = 3, CTL_T
        CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_TICKET_NN = 7, CTL_COMM_TIMEOUT = 8, CTL_TICKET_BBOX = 9, CTL_N = 12 };
 
 // ---- peer-memory exchange (multi-GPU, one process per GPU) ---------------------------------------
-// Every rank owns one mailbox in its HBM, mapped into all peers through CUDA IPC.  An exchange with
-// sequence number q posts this rank's doubles into slot [q & 1][rank] of EVERY rank's mailbox (plain
+// Every rank owns one mailbox in its HBM, mapped into all peers through CUDA IPC.  The exchange number q is kept
+// on the device (seq_local, advanced by the kernel that exchanges), so it is the same on every rank by
+// construction.  Exchange q posts this rank's doubles into slot [q & 1][rank] of EVERY rank's mailbox (plain
 // stores over NVLink), then publishes q in the matching flag with a system-scope release; the reader
 // spins on its own flags (acquire) and adds the slots in rank order, so every rank obtains the
 // bit-identical sum without a separate collective launch.
@@ -43,6 +44,7 @@ constexpr int PEER_SLOT = 32;                       // doubles per (parity, sour
 struct PeerMailbox {
     double data[2][PEER_MAX_WORLD][PEER_SLOT];
     unsigned long long flag[2][PEER_MAX_WORLD];
+    unsigned long long seq_local;                   // exchanges completed by the OWNER of this mailbox (peers never touch it)
 };
 struct PeerComm {
     PeerMailbox* box[PEER_MAX_WORLD];               // box[r] = rank r's mailbox as mapped in this process
@@ -84,7 +86,7 @@ struct NNScratch {
 // All launch on `st`, none synchronises.  `ctl` is the device control block; kernels return at entry
 // when ctl[CTL_DONE] != 0 and `honor_done` is set (used by the device-side loop).
 void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc, const int* ctl, int honor_done,
-                      cudaStream_t st);
+                      cudaStream_t st, int* progress = nullptr);
 void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                       cudaStream_t st);
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
@@ -92,26 +94,23 @@ void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, 
 int nn_exact_batch_points();
 
 // xf_fused != nullptr: the last block also runs the Horn solve (K3) into xf_fused (single-GPU path).
-// peer != nullptr (multi-GPU): the LAST block exchanges the sums with all peers inside the kernel (exchange
-// number `seq`) before it solves / closes the iteration; every rank ends up with bit-identical values.
+// peer != nullptr (multi-GPU): the LAST block exchanges the sums with all peers inside the kernel before it solves / closes the iteration; every rank ends up with bit-identical values.
 void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, int* ctl,
-                    int honor_done, double* xf_fused, cudaStream_t st, const PeerComm* peer = nullptr,
-                    unsigned long long seq = 0);
+                    int honor_done, double* xf_fused, cudaStream_t st, const PeerComm* peer = nullptr);
 void launch_solve(const ModelDev& m, const double* mom, double* xf, const int* ctl, int honor_done, cudaStream_t st);
 // in_place: p <- sR p + t (FP64 master and FP32 shadow).  finish: the last block also closes the iteration
 // (err_hist[it] = 2*sum/n, done flag, iteration counter) — single-GPU loop only.
 void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, int in_place, double* partials,
                       int n_blocks, double* err_sum, int* ctl, int honor_done, int finish, double n_global,
-                      double threshold, double* err_hist, cudaStream_t st, const PeerComm* peer = nullptr,
-                      unsigned long long seq = 0);
+                      double threshold, double* err_hist, cudaStream_t st, const PeerComm* peer = nullptr);
 // K2 + K3 + K4 in ONE cooperative launch (moments -> grid barrier -> Horn solve in every block -> transform
 // + residual -> last block closes the iteration).  `peer` (world > 1): the 18 moment sums and the residual
 // are exchanged through peer mailboxes inside the kernel; seq = sequence number of the first exchange.
 // Returns a cudaError_t (cooperative launch can fail).
 int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, double* xf,
                        double* err_sum, int* ctl, int honor_done, int in_place, int finish, double n_global,
-                       double threshold, double* err_hist, const PeerComm* peer, unsigned long long seq,
-                       unsigned long long* trace, cudaStream_t st);
+                       double threshold, double* err_hist, const PeerComm* peer, unsigned long long* trace,
+                       cudaStream_t st);
 int align_fused_max_blocks(int sm_count);
 void launch_finish(const double* err_sum, double n_global, double threshold, double* err_hist, int* ctl,
                    cudaStream_t st);

@@ -94,8 +94,13 @@ __global__ void __launch_bounds__(NN_THREADS, 4)
 nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx, const float* __restrict__ phy,
                  const float* __restrict__ phz, int np_pad, int n_tiles, int cpt,
                  float* __restrict__ out_best, float* __restrict__ out_runner, uint32_t* __restrict__ out_chunk,
-                 const int* __restrict__ ctl, int honor_done)
+                 const int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
 {
+    // Loop progress for the host (icp_run keeps only a few iterations enqueued ahead of the device): `progress`
+    // points into mapped pinned host memory, one word = (iterations closed << 1) | converged.  Published here, at
+    // the START of the next iteration, so that the PCIe write drains under this kernel instead of at a kernel end.
+    if (progress != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
+        *reinterpret_cast<volatile int*>(progress) = (ctl[CTL_ITERS] << 1) | (ctl[CTL_DONE] != 0);
     if (honor_done && ctl[CTL_DONE]) return;
 
     extern __shared__ __align__(128) unsigned char smem[];
@@ -536,7 +541,7 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
 }  // namespace
 
 void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc, const int* ctl, int honor_done,
-                      cudaStream_t st)
+                      cudaStream_t st, int* progress)
 {
     static bool attr_set = false;
     if (!attr_set) {
@@ -545,7 +550,7 @@ void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
     }
     nn_filter_kernel<<<sc.n_cta, NN_THREADS, FILTER_SMEM, st>>>(m.mhat, s.phx, s.phy, s.phz, (int)s.np_pad,
                                                                 (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.best,
-                                                                sc.runner, sc.chunk, ctl, honor_done);
+                                                                sc.runner, sc.chunk, ctl, honor_done, progress);
 }
 
 void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
