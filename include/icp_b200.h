@@ -106,7 +106,9 @@ int icp_get_transform(icp_ctx* ctx, double* s, double R[9], double t[3]);
  * error value (src/cpu.cc:65-73: (err_alignment + err_compute) / np) is < threshold
  * (reference: 1e-5, src/cpu.hh:113).  err_hist (nullable, max_iter doubles) receives the value the
  * reference prints each iteration.  check_sizes != 0 applies alignement_check (src/cpu.cc:42-53)
- * and returns ICP_ERR_SIZE_MISMATCH / ICP_ERR_TOO_FEW where the reference exits. */
+ * and returns ICP_ERR_SIZE_MISMATCH / ICP_ERR_TOO_FEW where the reference exits.
+ * The convergence test runs on the device; the host only throttles how far ahead it enqueues
+ * (ICP_LOOKAHEAD iterations, default 3, read at icp_create; 0 = enqueue all max_iter at once). */
 int icp_run(icp_ctx* ctx, int max_iter, double threshold, int check_sizes, int* iters_done, double* err_hist);
 
 /* Correspondence indices of the last closest pass (any of icp_closest / icp_run). */
