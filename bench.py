@@ -199,6 +199,11 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+NN_DESC = {"brute": "exact brute force (every pair evaluated)",
+           "tree": "exact bounding-box hierarchy (ICP_NN_TREE): identical indices; evals/s counts the np*nm pairs a brute-force "
+                   "search would evaluate, not executed work - compare icp_iterations_per_sec"}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import icp_b200
@@ -325,8 +330,8 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": args.workload, "description": desc, "np_per_gpu": len(p), "nm": len(m),
                    "sharding": "1 GPU" if world == 1 else f"scene = {world} shards of ~{len(p)} points "
                    f"({p_global_n} in total), model replicated, {comm_kind}",
-                   "l2": "flushed between steps (256 MB write)", "model_splits": st["n_splits"]},
-        "roofline": {"bound": "fp32", "kernel": "nn_filter_kernel", "achieved": achieved, "peak": peak,
+                   "l2": "flushed between steps (256 MB write)", "model_splits": st["n_splits"], "nn": NN_DESC[args.nn]},
+        "roofline": None if args.nn == "tree" else {"bound": "fp32", "kernel": "nn_filter_kernel", "achieved": achieved, "peak": peak,
                      "unit": "TFLOP/s", "frac": achieved / peak, "peak_source": peak_src,
                      "algorithmic_flops_per_eval": 8, "evals_per_launch": len(m) * len(p),
                      "avg_launch_ms": filt_ms_per_launch,
@@ -392,7 +397,7 @@ def run_batch(args, rank, world, local_rank, torch, dist):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32 filter + f64 re-rank/alignment", "data": "synthetic",
                 "pairs_per_sec": args.pairs / sec, "icp_iterations_per_sec": iters / sec,
                 "config": {"workload": args.workload, "pairs": args.pairs, "points_per_cloud": n, "max_iter": max_iter,
-                           "lanes_per_gpu": args.lanes, "sharding": f"pair-per-GPU, {world} GPU(s), no communication",
+                           "lanes_per_gpu": args.lanes, "nn": NN_DESC[args.nn], "sharding": f"pair-per-GPU, {world} GPU(s), no communication",
                            "l2": "each pair's clouds are uploaded from host memory inside the step (inputs > L2 in aggregate)"},
                 "roofline": None, "cpu_baseline": None,
                 "e2e": {"value": evals / sec, "unit": "evals/s", "h2d_bytes_per_step": args.pairs * 2 * n * 24,
@@ -414,10 +419,17 @@ def main():
     ap.add_argument("--max-iter", type=int, default=None, help="override the workload's max_iter")
     ap.add_argument("--pairs", type=int, default=64, help="batch workloads: cloud pairs in total (dealt round-robin to the ranks)")
     ap.add_argument("--lanes", type=int, default=3, help="batch workloads: concurrent contexts per GPU")
+    ap.add_argument("--nn", default="brute", choices=["brute", "tree"],
+                    help="brute: the exact brute-force search BASELINE.json's metric is quoted on (default); tree: the exact "
+                         "bounding-box-hierarchy search (SURVEY 8f-4) - same results, `value` then counts brute-force-EQUIVALENT pairs")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank holds a full copy of the scene as its shard (per-GPU work fixed); "
                          "strong = the one scene is cut into N contiguous blocks")
     args = ap.parse_args()
+    if args.nn == "tree":
+        os.environ["ICP_NN"] = "tree"        # read by icp_create (every context, batch lanes included)
+    elif os.environ.get("ICP_NN") == "tree":
+        args.nn = "tree"
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -97,6 +97,13 @@ struct icp_ctx {
     int n_red_blocks = 1;
     uint32_t *d_keys = nullptr, *d_keys_alt = nullptr; int32_t* d_vals = nullptr; void* d_cub = nullptr;
     size_t cub_bytes = 0, sort_cap = 0;
+    int32_t* d_vals_alt = nullptr;         // sorted values of the model's Morton sort (tree build)
+    // exact tree search, opt-in: ICP_NN=tree / icp_set_nn_mode
+    int nn_mode = ICP_NN_BRUTE;
+    TreeDev tree;
+    bool tree_built = false;
+    int tree_form = 0;                     // ICP_TREE: 0 auto, 1 wide (warp per point, 32-ary), 2 binary (thread per point)
+    double h_Rm = 0.0;                     // geo[3] of the current model (the tree needs 1e-12 <= Rm <= 1e12)
     int32_t* d_idx_out = nullptr; size_t idx_out_cap = 0;
     bool have_model = false, have_scene = false, have_idx = false;
     icp_stats stats{};
@@ -129,6 +136,58 @@ int ensure_stage(icp_ctx* c, size_t doubles)
     dfree(c->d_stage);
     CK(cudaMalloc((void**)&c->d_stage, doubles * sizeof(double)));
     c->stage_cap = doubles;
+    return ICP_OK;
+}
+
+// Radix-sort scratch (keys, values, cub temporary) for n items; grows only.
+int ensure_sort(icp_ctx* c, size_t n)
+{
+    if (c->sort_cap >= n) return ICP_OK;
+    int r;
+    if ((r = dalloc(&c->d_keys, n)) || (r = dalloc(&c->d_keys_alt, n)) || (r = dalloc(&c->d_vals, n)) ||
+        (r = dalloc(&c->d_vals_alt, n)))
+        return r;
+    const size_t bytes = tree_sort_bytes((int)n);
+    if (c->d_cub) cudaFree(c->d_cub);
+    c->d_cub = nullptr;
+    CK(cudaMalloc(&c->d_cub, bytes ? bytes : 1));
+    c->cub_bytes = bytes;
+    c->sort_cap = n;
+    return ICP_OK;
+}
+
+// Rm = 0: every model point coincides with c0; the surrogate is then the same for all of them and FP64 decides.
+bool tree_active(const icp_ctx* c)
+{
+    return c->nn_mode == ICP_NN_TREE && (c->h_Rm == 0.0 || (c->h_Rm >= 1e-12 && c->h_Rm <= 1e12));
+}
+
+// Builds the model's bounding-box hierarchy on first use after icp_set_model (tree mode only).
+int ensure_tree(icp_ctx* c)
+{
+    if (!tree_active(c) || c->tree_built) return ICP_OK;
+    int r;
+    const int64_t leaves = (c->m.nm + TREE_LEAF - 1) / TREE_LEAF;
+    int nl = 1;
+    while (nl < leaves) nl *= 2;
+    if (c->tree.cap_leaves < (size_t)nl) {
+        if ((r = dalloc(&c->tree.nodes, (size_t)nl * 2 * 6)) || (r = dalloc(&c->tree.pts, (size_t)nl * TREE_LEAF))) return r;
+        c->tree.cap_leaves = (size_t)nl;
+    }
+    c->tree.n_leaves = nl;
+    const size_t wfloats = wtree_plan(c->m.nm, c->tree.w);
+    if (c->tree.cap_wboxes < wfloats) {
+        if ((r = dalloc(&c->tree.wboxes, wfloats))) return r;
+        c->tree.cap_wboxes = wfloats;
+    }
+    if (c->tree.cap_wpts < (size_t)c->tree.w.count[0] * 32) {
+        if ((r = dalloc(&c->tree.wpts, (size_t)c->tree.w.count[0] * 32))) return r;
+        c->tree.cap_wpts = (size_t)c->tree.w.count[0] * 32;
+    }
+    if ((r = ensure_sort(c, (size_t)c->m.nm))) return r;
+    const int e = tree_build(c->m, c->tree, c->d_keys, c->d_keys_alt, c->d_vals, c->d_vals_alt, c->d_cub, c->cub_bytes, c->st);
+    if (e != 0) { g_err = std::string("tree_build: ") + cudaGetErrorString((cudaError_t)e); return ICP_ERR_CUDA; }
+    c->tree_built = true;
     return ICP_OK;
 }
 
@@ -180,11 +239,27 @@ int allreduce(icp_ctx* c, double* buf, size_t n)
     return ICP_OK;
 }
 
-// One closest-matrix pass (K1) on the stream.
-void nn_pass(icp_ctx* c, int honor_done, cudaEvent_t e0, cudaEvent_t e1, cudaEvent_t e2 = nullptr,
+// One closest-matrix pass (K1) on the stream.  use_prev: idx[] holds valid matches of the same model (tree mode
+// starts every search from them).
+void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent_t e1, cudaEvent_t e2 = nullptr,
              cudaEvent_t e3 = nullptr)
 {
     if (e0) cudaEventRecord(e0, c->st);
+    if (tree_active(c) && c->tree_built) {
+        // measured (profiles/r01h_tree.md): a warp per point wins while the grid is a few waves (cow 0.014 vs 0.052 ms,
+        // horse 128 vs 285 us per search: the slowest thread no longer sets the kernel time); a thread per point
+        // wins once there are enough points to fill the machine either way (2^18: 0.19 vs 0.47 ms, 2^22: 2x)
+        const bool wide = c->tree_form == 1 || (c->tree_form == 0 && c->s.np <= 131072);
+        if (wide)
+            launch_nn_wtree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
+        else
+            launch_nn_tree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
+        if (e1) cudaEventRecord(e1, c->st);
+        if (e2) cudaEventRecord(e2, c->st);
+        if (e3) cudaEventRecord(e3, c->st);
+        c->stats.kernels_launched += 1;
+        return;
+    }
     launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st, c->progress_arg);
     if (e1) cudaEventRecord(e1, c->st);
     launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
@@ -327,6 +402,8 @@ int icp_create(icp_ctx** out, int device)
     if (const char* e = getenv("ICP_ALIGN")) c->align_mode = !strcmp(e, "fused") ? 1 : (!strcmp(e, "split") ? 2 : 0);
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
+    if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
+    if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
@@ -353,7 +430,7 @@ void icp_destroy(icp_ctx* c)
     dfree(c->sc.seg_v); dfree(c->sc.seg_k); dfree(c->sc.batch_ticket);
     dfree(c->d_stage); dfree(c->d_partials); dfree(c->d_mom); dfree(c->d_xf); dfree(c->d_err_sum); dfree(c->d_out6);
     dfree(c->d_err_hist); dfree(c->d_ctl); dfree(c->d_keys); dfree(c->d_keys_alt); dfree(c->d_vals);
-    dfree(c->d_idx_out);
+    dfree(c->d_idx_out); dfree(c->d_vals_alt); dfree(c->tree.nodes); dfree(c->tree.pts); dfree(c->tree.wboxes); dfree(c->tree.wpts);
     if (c->d_cub) cudaFree(c->d_cub);
     for (auto e : c->ev_filter) cudaEventDestroy(e);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -381,7 +458,9 @@ int icp_set_model(icp_ctx* c, const double* m_xyz, int64_t nm)
     launch_model_geo(c->m.geo, c->st);
     launch_model_build(c->d_stage, c->m, c->st);
     CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(&c->h_Rm, c->m.geo + 3, sizeof(double), cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
+    c->tree_built = false;
     c->have_model = true;
     c->have_idx = false;
     c->stats.nm = nm;
@@ -418,18 +497,7 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
         CK(cudaMemsetAsync(c->sc.batch_ticket, 0, n_tickets * sizeof(int), c->st));
     }
     // Morton sort of the scene (once per scene; a similarity transform keeps tiles compact)
-    if (c->sort_cap < (size_t)np) {
-        if ((r = dalloc(&c->d_keys, (size_t)np)) || (r = dalloc(&c->d_keys_alt, (size_t)np)) ||
-            (r = dalloc(&c->d_vals, (size_t)np)))
-            return r;
-        size_t bytes = 0;
-        cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->d_keys, c->d_keys_alt, c->d_vals, c->s.perm, (int)np, 0, 30,
-                                        c->st);
-        if (c->d_cub) cudaFree(c->d_cub);
-        CK(cudaMalloc(&c->d_cub, bytes ? bytes : 1));
-        c->cub_bytes = bytes;
-        c->sort_cap = (size_t)np;
-    }
+    if ((r = ensure_sort(c, (size_t)np))) return r;
     double* bbox = c->d_stage + (size_t)np * 3;
     launch_bbox(c->d_stage, np, bbox, c->d_partials, c->sm_count * 2, c->d_ctl, c->st);
     launch_scene_keys(c->d_stage, np, bbox, c->d_keys, c->d_vals, c->st);
@@ -457,6 +525,19 @@ int icp_reset_scene(icp_ctx* c)
     if ((r = ensure_scratch(c))) return r;
     c->have_idx = false;
     return set_identity_xf(c);
+}
+
+int icp_set_nn_mode(icp_ctx* c, int mode)
+{
+    if (!c || (mode != ICP_NN_BRUTE && mode != ICP_NN_TREE)) { g_err = "icp_set_nn_mode: bad arguments"; return ICP_ERR_INVALID; }
+    c->nn_mode = mode;
+    return ICP_OK;
+}
+
+int icp_get_nn_mode(icp_ctx* c)
+{
+    if (!c) return ICP_ERR_INVALID;
+    return tree_active(c) || (c->nn_mode == ICP_NN_TREE && !c->have_model) ? ICP_NN_TREE : ICP_NN_BRUTE;
 }
 
 int icp_get_scene(icp_ctx* c, double* out)
@@ -492,9 +573,10 @@ int icp_closest(icp_ctx* c, int32_t* idx_out, double* Y_out)
     CK(cudaSetDevice(c->device));
     int r;
     if ((r = reset_ctl(c))) return r;
+    if ((r = ensure_tree(c))) return r;
     c->stats.kernels_launched = 0;
     CK(cudaEventRecord(c->ev0, c->st));
-    nn_pass(c, 0, nullptr, nullptr);
+    nn_pass(c, 0, c->have_idx ? 1 : 0, nullptr, nullptr);
     CK(cudaEventRecord(c->ev1, c->st));
     CK(cudaGetLastError());
     c->have_idx = true;
@@ -630,6 +712,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
         c->ev_filter.push_back(e);
     }
     if ((r = reset_ctl(c))) return r;
+    if ((r = ensure_tree(c))) return r;
     c->stats.kernels_launched = 0;
     CK(cudaEventRecord(c->ev0, c->st));
     // The host runs ahead of the device and cannot know when the loop converges, so every kernel returns at entry
@@ -650,7 +733,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
             if (w) break;
         }
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
-        nn_pass(c, 1, ev[0], ev[1], c->profile ? ev[2] : nullptr, c->profile ? ev[3] : nullptr);
+        nn_pass(c, 1, (it > 0 || c->have_idx) ? 1 : 0, ev[0], ev[1], c->profile ? ev[2] : nullptr, c->profile ? ev[3] : nullptr);
         if (!nccl_path(c)) {
             int launched = align_step(c, 1, 1, 1, np_glob, threshold);
             if (launched < 0) return launched;
@@ -735,12 +818,21 @@ int icp_get_stats(icp_ctx* c, icp_stats* out)
 
 static thread_local icp_ctx* t_oneshot = nullptr;
 
+// Hidden contexts (the one-shot wrappers' and icp_batch_run's lanes) outlive a call: they follow the environment
+// as it is when they are used, not as it was when they were created.
+static void apply_env_nn(icp_ctx* c)
+{
+    const char* e = getenv("ICP_NN");
+    c->nn_mode = (e && !strcmp(e, "tree")) ? ICP_NN_TREE : ICP_NN_BRUTE;
+}
+
 static int oneshot_ctx(icp_ctx** out)
 {
     if (!t_oneshot) {
         int r = icp_create(&t_oneshot, 0);
         if (r) { t_oneshot = nullptr; return r; }
     }
+    apply_env_nn(t_oneshot);
     *out = t_oneshot;
     return ICP_OK;
 }
@@ -894,7 +986,7 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     auto worker = [&]() {
         icp_ctx* c = lane_pool_take(device);       // contexts survive between calls: no per-call cudaMalloc storm
         int r = c ? ICP_OK : icp_create(&c, device);
-        if (c) c->is_lane = true;
+        if (c) { c->is_lane = true; apply_env_nn(c); }
         std::vector<double> hist((size_t)(max_iter > 0 ? max_iter : 1));
         while (!r && status.load() == ICP_OK) {
             const int64_t k = next.fetch_add(1);

@@ -82,6 +82,24 @@ struct NNScratch {
     size_t cap_points = 0;       // allocated n_splits * np_pad
 };
 
+// Bounding-box hierarchy over the Morton-sorted model (tree_kernels.cu; opt-in exact search).
+constexpr int TREE_LEAF = 8;     // model points per leaf
+struct WideLevels {              // 32-ary form: level 0 = boxes of the 32-point leaves, level l = boxes of level l-1's blocks
+    int T = 0;                   // number of box levels; the top one is a single block of <= 32 boxes
+    int count[8] = {};           // boxes at each level
+    long long off[8] = {};       // float offset of each level's blocks (192 floats per block of 32 boxes) in wboxes
+};
+struct TreeDev {
+    int n_leaves = 0;            // power of two >= ceil(nm / TREE_LEAF); 0 = not built
+    float* nodes = nullptr;      // [2 * n_leaves][6]  lo.xyz, hi.xyz; heap numbering, root = 1, leaves n_leaves..2n-1
+    float4* pts = nullptr;       // [n_leaves * TREE_LEAF]  (m^.x, m^.y, m^.z, original index), Morton order
+    size_t cap_leaves = 0;
+    WideLevels w;
+    float* wboxes = nullptr;     // all levels of the wide form
+    float4* wpts = nullptr;      // [count[0] * 32] sorted points, padded with the last one
+    size_t cap_wboxes = 0, cap_wpts = 0;
+};
+
 // ---- launchers (defined in nn_kernels.cu / align_kernels.cu) ------------------------------------
 // All launch on `st`, none synchronises.  `ctl` is the device control block; kernels return at entry
 // when ctl[CTL_DONE] != 0 and `honor_done` is set (used by the device-side loop).
@@ -92,6 +110,15 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                      int sm_count, cudaStream_t st, unsigned long long* trace = nullptr);
 int nn_exact_batch_points();
+// tree search (tree_kernels.cu).  tree_build returns a cudaError_t; use_prev: idx[] holds the previous matches.
+size_t tree_sort_bytes(int n);
+int tree_build(const ModelDev& m, TreeDev& t, uint32_t* keys, uint32_t* keys_alt,
+               int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, cudaStream_t st);
+size_t wtree_plan(int64_t nm, WideLevels& w);
+void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int use_prev, int* ctl, int honor_done,
+                     cudaStream_t st, int* progress = nullptr);
+void launch_nn_tree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int use_prev, int* ctl, int honor_done,
+                    cudaStream_t st, int* progress = nullptr);
 
 // xf_fused != nullptr: the last block also runs the Horn solve (K3) into xf_fused (single-GPU path).
 // peer != nullptr (multi-GPU): the LAST block exchanges the sums with all peers inside the kernel before it solves / closes the iteration; every rank ends up with bit-identical values.
@@ -135,6 +162,15 @@ int reduce_blocks_for(int64_t n, int sm_count);
 
 // ---- small device helpers -----------------------------------------------------------------------
 #ifdef __CUDACC__
+// Loop progress for the host (icp_run keeps only a few iterations enqueued ahead of the device): `progress`
+// points into mapped pinned host memory, one word = (iterations closed << 1) | converged.  Called at the entry of
+// the FIRST kernel of an iteration, so that the PCIe write drains under that kernel instead of at a kernel end.
+__device__ __forceinline__ void publish_progress(int* progress, const int* ctl)
+{
+    if (progress != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
+        *reinterpret_cast<volatile int*>(progress) = (ctl[CTL_ITERS] << 1) | (ctl[CTL_DONE] != 0);
+}
+
 __device__ __forceinline__ double warp_sum(double v)
 {
 #pragma unroll

@@ -96,11 +96,7 @@ nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx,
                  float* __restrict__ out_best, float* __restrict__ out_runner, uint32_t* __restrict__ out_chunk,
                  const int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
 {
-    // Loop progress for the host (icp_run keeps only a few iterations enqueued ahead of the device): `progress`
-    // points into mapped pinned host memory, one word = (iterations closed << 1) | converged.  Published here, at
-    // the START of the next iteration, so that the PCIe write drains under this kernel instead of at a kernel end.
-    if (progress != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
-        *reinterpret_cast<volatile int*>(progress) = (ctl[CTL_ITERS] << 1) | (ctl[CTL_DONE] != 0);
+    publish_progress(progress, ctl);
     if (honor_done && ctl[CTL_DONE]) return;
 
     extern __shared__ __align__(128) unsigned char smem[];

@@ -1,0 +1,473 @@
+// tree_kernels.cu — EXACT nearest neighbour through a bounding-box hierarchy over the Morton-sorted model
+// ("exact spatial acceleration behind the same icp_closest").  Opt-in (icp_set_nn_mode /
+// ICP_NN=tree); the brute-force filter of nn_kernels.cu stays the default and the headline of bench.py.
+//
+// Same contract as the brute-force path: idx[j] = the FIRST minimum over k of the reference's FP64 value
+// v_k = sqrt(pow(dx,2)+pow(dy,2)+pow(dz,2)) (src/cpu.cc:16-22), bit-exact.  How exactness is kept:
+//   * the tree is searched with an FP32 surrogate d~2_k = fl32(|p^ - m^_k|^2) of the centred FP32 shadows
+//     (p^ = fl32(p - c0), m^ = fl32(m - c0));
+//   * with u = 2^-24:  sqrt(d~2) = D^(1 +- 3u),  |D - D^| <= E = u(1+3u)(|p^| + Rm)   (D = true distance), and the
+//     reference's v_k = D_k(1 +- 4*2^-53).  If k0 minimises the surrogate and k* is ANY index attaining the
+//     reference's minimum, then  D^_k* <= D^_k0 + 2E(1+eps)  and therefore
+//         d~2_k*  <=  thr2 := ( sqrt(best2)(1+3u) + 2E )^2 (1+16u)         (best2 = d~2_k0)
+//     thr2 is evaluated with every operation rounded UP and is monotone in best2, so the running thr2 of a
+//     search in progress is always >= the final one;
+//   * every model point met with d~2 <= thr2 is evaluated in FP64 with the reference's own expression and
+//     merged by (v, lowest index) — order independent, hence the traversal order is free;
+//   * a node is skipped only when a LOWER bound of its box distance (all operations rounded DOWN) exceeds
+//     thr2, which (1+16u) keeps above d~2 of every point inside the box.
+// Model scales outside [1e-12, 1e12] are refused at build time (FP32 squares would leave the normal range);
+// icp_api.cu then keeps the brute-force path, whose bound has no such restriction.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "icp_common.cuh"
+
+namespace icpb {
+namespace {
+
+constexpr int TREE_THREADS = 128;
+constexpr int TREE_STACK = 40;
+
+__device__ __forceinline__ double ref_dist2(double px, double py, double pz, double mx, double my, double mz)
+{
+    const double dx = __dsub_rn(px, mx), dy = __dsub_rn(py, my), dz = __dsub_rn(pz, mz);
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+__device__ __forceinline__ uint32_t tree_spread10(uint32_t v)
+{
+    v &= 0x3ffu;
+    v = (v | (v << 16)) & 0x030000ffu;
+    v = (v | (v << 8)) & 0x0300f00fu;
+    v = (v | (v << 4)) & 0x030c30c3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+
+// 30-bit Morton keys of the centred FP32 model over its bounding box (geo[4..9] = bbox, geo[0..2] = c0)
+__global__ void tree_keys_kernel(const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
+                                 uint32_t* __restrict__ keys, int32_t* __restrict__ vals)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nm) return;
+    const float4 m = mhat[i];
+    const float v[3] = {m.x, m.y, m.z};
+    uint32_t q[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float lo = (float)(geo[4 + c] - geo[c]), ext = (float)(geo[7 + c] - geo[4 + c]);
+        float f = ext > 0.0f ? (v[c] - lo) / ext : 0.0f;
+        f = fminf(fmaxf(f, 0.0f), 1.0f);
+        q[c] = (uint32_t)fminf(f * 1024.0f, 1023.0f);
+    }
+    keys[i] = (tree_spread10(q[0]) << 2) | (tree_spread10(q[1]) << 1) | tree_spread10(q[2]);
+    vals[i] = i;
+}
+
+// sorted leaf points: (m^.x, m^.y, m^.z, original index); positions >= nm repeat the last valid point
+__global__ void tree_points_kernel(const float4* __restrict__ mhat, const int32_t* __restrict__ perm, int nm,
+                                   int n_slots, float4* __restrict__ pts)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_slots) return;
+    const int k = perm[i < nm ? i : nm - 1];
+    const float4 m = mhat[k];
+    pts[i] = make_float4(m.x, m.y, m.z, __int_as_float(k));
+}
+
+// node = 6 floats (lo.xyz, hi.xyz); heap numbering: root 1, children 2i / 2i+1, leaves NL .. 2NL-1
+// Leaves past the last model point get the EMPTY box (lo = +inf, hi = -inf): its distance is +inf, above every
+// finite threshold, and it is neutral under the min/max of tree_level_kernel.
+__global__ void tree_leaf_boxes_kernel(const float4* __restrict__ pts, int n_leaves, int n_real, float* __restrict__ nodes)
+{
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n_leaves) return;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int i = 0; i < TREE_LEAF && l < n_real; ++i) {
+        const float4 q = pts[(size_t)l * TREE_LEAF + i];
+        lo[0] = fminf(lo[0], q.x); hi[0] = fmaxf(hi[0], q.x);
+        lo[1] = fminf(lo[1], q.y); hi[1] = fmaxf(hi[1], q.y);
+        lo[2] = fminf(lo[2], q.z); hi[2] = fmaxf(hi[2], q.z);
+    }
+    float* o = nodes + (size_t)(n_leaves + l) * 6;
+    o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2]; o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
+}
+
+__global__ void tree_level_kernel(float* __restrict__ nodes, int first, int count)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const size_t i = (size_t)first + t;
+    const float* a = nodes + 2 * i * 6;
+    const float* b = a + 6;
+    float* o = nodes + i * 6;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        o[c] = fminf(a[c], b[c]);
+        o[3 + c] = fmaxf(a[3 + c], b[3 + c]);
+    }
+}
+
+// lower bound of the squared distance from p to the box, every operation rounded down
+__device__ __forceinline__ float box_dist2_rd(float px, float py, float pz, float lx, float ly, float lz, float hx,
+                                              float hy, float hz)
+{
+    const float ex = fmaxf(fmaxf(__fsub_rd(lx, px), __fsub_rd(px, hx)), 0.0f);
+    const float ey = fmaxf(fmaxf(__fsub_rd(ly, py), __fsub_rd(py, hy)), 0.0f);
+    const float ez = fmaxf(fmaxf(__fsub_rd(lz, pz), __fsub_rd(pz, hz)), 0.0f);
+    return __fmaf_rd(ez, ez, __fmaf_rd(ey, ey, __fmul_rd(ex, ex)));
+}
+
+struct TreeQuery {
+    float px, py, pz;        // p^
+    double qx, qy, qz;       // p (FP64 master)
+    float twoE;              // 2E, rounded up
+    float best2, thr2;       // running surrogate minimum and acceptance threshold
+    double v;                // running reference minimum (v, k), lexicographic
+    int k;
+    const double *m64x, *m64y, *m64z;
+
+    __device__ __forceinline__ void set_best(float b2)
+    {
+        best2 = b2;
+        const float r = __fmul_ru(__fsqrt_ru(b2), 1.0000002f);            // (1 + 3u) < 1.0000002
+        const float a = __fadd_ru(r, twoE);
+        thr2 = __fmul_ru(__fmul_ru(a, a), 1.000001f);                     // (1 + 16u) < 1.000001
+    }
+    __device__ __forceinline__ void offer(float d2, int kk)
+    {
+        if (d2 <= thr2) {
+            if (d2 < best2) set_best(d2);
+            const double vv = __dsqrt_rn(ref_dist2(qx, qy, qz, m64x[kk], m64y[kk], m64z[kk]));
+            if (vv < v || (vv == v && kk < k)) { v = vv; k = kk; }
+        }
+    }
+};
+
+__device__ __forceinline__ float surrogate_direct(float px, float py, float pz, float mx, float my, float mz)
+{
+    const float dx = __fsub_rn(px, mx), dy = __fsub_rn(py, my), dz = __fsub_rn(pz, mz);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
+
+__global__ void __launch_bounds__(TREE_THREADS)
+nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, int n_leaves /* power of two */,
+               const float4* __restrict__ mhat, const double* __restrict__ m64x, const double* __restrict__ m64y,
+               const double* __restrict__ m64z, const double* __restrict__ geo, const double* __restrict__ p64x,
+               const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
+               const float* __restrict__ phy, const float* __restrict__ phz, int np, int nm,
+               int32_t* __restrict__ idx, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
+{
+    publish_progress(progress, ctl);
+    if (honor_done && ctl[CTL_DONE]) return;
+    const int j = blockIdx.x * TREE_THREADS + threadIdx.x;
+    if (j >= np) return;
+
+    TreeQuery q;
+    q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
+    q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
+    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    {
+        const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
+        const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
+        // 2E = 2 u (1+3u) (|p^| + Rm), plus an absolute floor against underflow
+        q.twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
+    }
+    q.best2 = q.thr2 = 3.4028235e38f;     // FLT_MAX, not +inf: the empty boxes of padded leaves (+inf) stay above it
+    q.v = __longlong_as_double(0x7ff0000000000000LL);
+    q.k = 0x7fffffff;
+    if (use_prev) {      // last iteration's match: a near-optimal bound before the first node is opened
+        const int kp = idx[j];
+        if (kp >= 0 && kp < nm) {
+            const float4 m = mhat[kp];
+            q.offer(surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z), kp);
+        }
+    }
+
+    int st_node[TREE_STACK];
+    float st_d[TREE_STACK];
+    int sp = 0;
+    int node = 1;
+    float nd = 0.0f;
+    const float4* nodes4 = reinterpret_cast<const float4*>(nodes);
+    for (;;) {
+        if (nd <= q.thr2) {
+            while (node < n_leaves) {                                 // internal: open both children, near one first
+                const float4 a = nodes4[(size_t)node * 3], b = nodes4[(size_t)node * 3 + 1],
+                             c = nodes4[(size_t)node * 3 + 2];        // children 2*node, 2*node+1 = 12 floats
+                const float d0 = box_dist2_rd(q.px, q.py, q.pz, a.x, a.y, a.z, a.w, b.x, b.y);
+                const float d1 = box_dist2_rd(q.px, q.py, q.pz, b.z, b.w, c.x, c.y, c.z, c.w);
+                const bool first0 = d0 <= d1;
+                const float dn = first0 ? d0 : d1, df = first0 ? d1 : d0;
+                const int near = 2 * node + (first0 ? 0 : 1), far = 2 * node + (first0 ? 1 : 0);
+                if (df <= q.thr2) {      // one push per level at most: sp <= log2(n_leaves) < TREE_STACK
+                    st_node[sp] = far; st_d[sp] = df; ++sp; }
+                node = near;
+                nd = dn;
+                if (!(dn <= q.thr2)) { node = -1; break; }
+            }
+            if (node >= n_leaves) {
+                const float4* lp = pts + (size_t)(node - n_leaves) * TREE_LEAF;
+#pragma unroll
+                for (int i = 0; i < TREE_LEAF; ++i) {
+                    const float4 m = lp[i];
+                    q.offer(surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z), __float_as_int(m.w));
+                }
+            }
+        }
+        if (sp == 0) break;
+        --sp;
+        node = st_node[sp];
+        nd = st_d[sp];
+    }
+    if (q.k == 0x7fffffff) {
+        // nothing was accepted: the FP32 surrogate overflowed (a scene point > 1e19 away from the model).  Plain
+        // FP64 scan in index order with the reference's expression, first minimum.
+        double bv = __longlong_as_double(0x7ff0000000000000LL);
+        q.k = 0;
+        for (int kk = 0; kk < nm; ++kk) {
+            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+            if (vv < bv) { bv = vv; q.k = kk; }
+        }
+    }
+    idx[j] = q.k;
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Wide form: 32-ary hierarchy, ONE WARP PER SCENE POINT.  Leaf = 32 consecutive Morton-sorted model points
+// (one per lane); a node = 32 child boxes stored as six 32-float rows (lo.x[32] .. hi.z[32]) so that the warp
+// reads them with six coalesced 128-byte loads and every lane measures one child.  The whole warp follows
+// one path (no divergence), the tree is 3 levels deep for horse and 4 for 2^22 points, and the per-level
+// cursor (node, remaining-children mask) lives in the registers of lane `level` — there is no stack in memory.
+// Same bound, same acceptance rule and same FP64 decision as the thread-per-point kernel above.
+constexpr int WT_WARPS = 8;     // scene points per CTA
+
+__global__ void wtree_leaf_boxes_kernel(const float4* __restrict__ pts, int n_leaves, int n_padded,
+                                        float* __restrict__ boxes0)
+{
+    const int l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (l >= n_padded) return;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (l < n_leaves) {
+        const float4 q = pts[(size_t)l * 32 + lane];
+        lo[0] = hi[0] = q.x; lo[1] = hi[1] = q.y; lo[2] = hi[2] = q.z;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+                hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+            }
+    }
+    if (lane == 0) {
+        float* blk = boxes0 + (size_t)(l >> 5) * 192 + (l & 31);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { blk[c * 32] = lo[c]; blk[(3 + c) * 32] = hi[c]; }
+    }
+}
+
+// box i of the upper level = union of the 32 child boxes in block i of the lower level
+__global__ void wtree_level_kernel(const float* __restrict__ lower, int n_upper, int n_padded, float* __restrict__ upper)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_padded) return;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (i < n_upper) {
+        const float* blk = lower + (size_t)i * 192;
+        for (int ch = 0; ch < 32; ++ch)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                lo[c] = fminf(lo[c], blk[c * 32 + ch]);
+                hi[c] = fmaxf(hi[c], blk[(3 + c) * 32 + ch]);
+            }
+    }
+    float* o = upper + (size_t)(i >> 5) * 192 + (i & 31);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { o[c * 32] = lo[c]; o[(3 + c) * 32] = hi[c]; }
+}
+
+__global__ void __launch_bounds__(WT_WARPS * 32)
+nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __restrict__ pts,
+                const float4* __restrict__ mhat, const double* __restrict__ m64x, const double* __restrict__ m64y,
+                const double* __restrict__ m64z, const double* __restrict__ geo, const double* __restrict__ p64x,
+                const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
+                const float* __restrict__ phy, const float* __restrict__ phz, int np, int nm,
+                int32_t* __restrict__ idx, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
+{
+    publish_progress(progress, ctl);
+    if (honor_done && ctl[CTL_DONE]) return;
+    const int lane = threadIdx.x & 31;
+    const int j = blockIdx.x * WT_WARPS + (threadIdx.x >> 5);
+    if (j >= np) return;                                    // warp-uniform
+    constexpr unsigned FULL = 0xffffffffu;
+
+    TreeQuery q;                                            // warp-uniform except (v, k), which are per lane
+    q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
+    q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
+    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    {
+        const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
+        const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
+        q.twoE = __fadd_ru(__fmul_ru(1.1920932e-7f, __fadd_ru(H, Rm)), 1.0e-30f);
+    }
+    q.best2 = q.thr2 = 3.4028235e38f;
+    q.v = __longlong_as_double(0x7ff0000000000000LL);
+    q.k = 0x7fffffff;
+    if (use_prev) {
+        const int kp = idx[j];
+        if (kp >= 0 && kp < nm) {
+            const float4 m = mhat[kp];
+            const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
+            q.set_best(d2);
+            if (lane == 0) {
+                q.v = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kp], m64y[kp], m64z[kp]));
+                q.k = kp;
+            }
+        }
+    }
+
+    // cursor of level l in lane l: block index at that level, children not yet opened
+    const long long my_off = lane < lv.T ? lv.off[lane] : 0;
+    int my_node = 0;
+    unsigned my_mask = FULL;
+    int lvl = lv.T - 1;
+    for (;;) {
+        const int b = __shfl_sync(FULL, my_node, lvl);
+        const unsigned msk = __shfl_sync(FULL, my_mask, lvl);
+        const float* blk = boxes + __shfl_sync(FULL, my_off, lvl) + (size_t)b * 192 + lane;
+        const float d = box_dist2_rd(q.px, q.py, q.pz, blk[0], blk[32], blk[64], blk[96], blk[128], blk[160]);
+        const unsigned alive = __ballot_sync(FULL, d <= q.thr2) & msk;
+        if (alive == 0u) {
+            if (++lvl >= lv.T) break;
+            continue;
+        }
+        if (lvl > 0) {
+            const unsigned key = ((alive >> lane) & 1u) ? ((__float_as_uint(d) & ~31u) | (unsigned)lane) : 0xffffffffu;
+            const int c = (int)(__reduce_min_sync(FULL, key) & 31u);        // nearest child first
+            if (lane == lvl) my_mask = alive & ~(1u << c);                   // thr2 only shrinks: the others stay out
+            --lvl;
+            if (lane == lvl) { my_node = b * 32 + c; my_mask = FULL; }
+            continue;
+        }
+        // lvl == 0: the children are leaves.  All of them are handled here, nearest first, with the box distances
+        // kept in registers; a leaf drops out as soon as the shrinking threshold passes its box.
+        unsigned rem = alive;
+        while (rem != 0u) {
+            const unsigned key = ((rem >> lane) & 1u) ? ((__float_as_uint(d) & ~31u) | (unsigned)lane) : 0xffffffffu;
+            const int c = (int)(__reduce_min_sync(FULL, key) & 31u);
+            const float4 m = pts[((size_t)b * 32 + c) * 32 + lane];
+            const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
+            const float dmin = __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(d2)));   // d2 >= 0: bits are monotone
+            if (dmin < q.best2) q.set_best(dmin);
+            if (d2 <= q.thr2) {
+                const int kk = __float_as_int(m.w);
+                const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+                if (vv < q.v || (vv == q.v && kk < q.k)) { q.v = vv; q.k = kk; }
+            }
+            rem &= ~(1u << c) & __ballot_sync(FULL, d <= q.thr2);
+        }
+        if (++lvl >= lv.T) break;
+    }
+    double v = q.v;
+    int k = q.k;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(FULL, v, o);
+        const int ok = __shfl_xor_sync(FULL, k, o);
+        if (ov < v || (ov == v && ok < k)) { v = ov; k = ok; }
+    }
+    if (k == 0x7fffffff) {       // FP32 surrogate overflowed (scene point > 1e19 away): FP64 scan, first minimum
+        v = __longlong_as_double(0x7ff0000000000000LL);
+        for (int kk = lane; kk < nm; kk += 32) {
+            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+            if (vv < v) { v = vv; k = kk; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ov = __shfl_xor_sync(FULL, v, o);
+            const int ok = __shfl_xor_sync(FULL, k, o);
+            if (ov < v || (ov == v && ok < k)) { v = ov; k = ok; }
+        }
+        if (k == 0x7fffffff) k = 0;
+    }
+    if (lane == 0) idx[j] = k;
+}
+
+}  // namespace
+
+// Builds the hierarchy for the model currently in `m` (mhat / geo valid); keys/vals/perm/cub: sort scratch for nm items.
+int tree_build(const ModelDev& m, TreeDev& t, uint32_t* keys, uint32_t* keys_alt,
+               int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, cudaStream_t st)
+{
+    const int nm = (int)m.nm;
+    tree_keys_kernel<<<(nm + 255) / 256, 256, 0, st>>>(m.mhat, nm, m.geo, keys, vals);
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys_alt, vals, perm, nm, 0, 30, st);
+    if (e != cudaSuccess) return (int)e;
+    const int n_slots = t.n_leaves * TREE_LEAF;
+    tree_points_kernel<<<(n_slots + 255) / 256, 256, 0, st>>>(m.mhat, perm, nm, n_slots, t.pts);
+    tree_leaf_boxes_kernel<<<(t.n_leaves + 255) / 256, 256, 0, st>>>(t.pts, t.n_leaves, (nm + TREE_LEAF - 1) / TREE_LEAF,
+                                                                     t.nodes);
+    for (int first = t.n_leaves / 2; first >= 1; first /= 2)
+        tree_level_kernel<<<(first + 255) / 256, 256, 0, st>>>(t.nodes, first, first);
+    // wide form (same sorted order)
+    const int n0 = t.w.count[0];
+    tree_points_kernel<<<(n0 * 32 + 255) / 256, 256, 0, st>>>(m.mhat, perm, nm, n0 * 32, t.wpts);
+    {
+        const int padded = (n0 + 31) / 32 * 32;
+        wtree_leaf_boxes_kernel<<<(padded * 32 + 255) / 256, 256, 0, st>>>(t.wpts, n0, padded, t.wboxes + t.w.off[0]);
+    }
+    for (int l = 1; l < t.w.T; ++l) {
+        const int padded = (t.w.count[l] + 31) / 32 * 32;
+        wtree_level_kernel<<<(padded + 127) / 128, 128, 0, st>>>(t.wboxes + t.w.off[l - 1], t.w.count[l], padded,
+                                                                 t.wboxes + t.w.off[l]);
+    }
+    return (int)cudaGetLastError();
+}
+
+// Level geometry of the wide tree for nm points; returns the number of floats the boxes need.
+size_t wtree_plan(int64_t nm, WideLevels& w)
+{
+    int64_t n = (nm + 31) / 32;          // leaves
+    size_t off = 0;
+    w.T = 0;
+    for (;;) {
+        const int64_t blocks = (n + 31) / 32;
+        w.count[w.T] = (int)n;
+        w.off[w.T] = (long long)off;
+        off += (size_t)blocks * 192;
+        ++w.T;
+        if (blocks == 1) break;
+        n = blocks;
+    }
+    return off;
+}
+
+void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int use_prev, int* ctl, int honor_done,
+                     cudaStream_t st, int* progress)
+{
+    const int grid = (int)((s.np + WT_WARPS - 1) / WT_WARPS);
+    nn_wtree_kernel<<<grid, WT_WARPS * 32, 0, st>>>(t.wboxes, t.w, t.wpts, m.mhat, m.m64x, m.m64y, m.m64z, m.geo, s.p64x,
+                                                    s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm, s.idx,
+                                                    use_prev, ctl, honor_done, progress);
+}
+
+size_t tree_sort_bytes(int n)
+{
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (uint32_t*)nullptr, (uint32_t*)nullptr, (int32_t*)nullptr,
+                                    (int32_t*)nullptr, n, 0, 30, (cudaStream_t)0);
+    return bytes;
+}
+
+void launch_nn_tree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int use_prev, int* ctl, int honor_done,
+                    cudaStream_t st, int* progress)
+{
+    const int grid = (int)((s.np + TREE_THREADS - 1) / TREE_THREADS);
+    nn_tree_kernel<<<grid, TREE_THREADS, 0, st>>>(t.nodes, t.pts, t.n_leaves, m.mhat, m.m64x, m.m64y, m.m64z, m.geo,
+                                                  s.p64x, s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm,
+                                                  s.idx, use_prev, ctl, honor_done, progress);
+}
+
+}  // namespace icpb

@@ -32,6 +32,7 @@ EXPORTS = [
     "icp_get_transform", "icp_run", "icp_get_indices", "icp_get_stats", "icp_closest_matrix_host",
     "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
     "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run", "icp_release_cached",
+    "icp_set_nn_mode", "icp_get_nn_mode",
 ]
 
 
@@ -77,6 +78,8 @@ def load_library(path=None):
     L.icp_set_scene.argtypes = [vp, _dp, C.c_int64]
     L.icp_get_scene.argtypes = [vp, _dp]
     L.icp_reset_scene.argtypes = [vp]
+    L.icp_set_nn_mode.argtypes = [vp, C.c_int]
+    L.icp_get_nn_mode.argtypes = [vp]
     L.icp_closest.argtypes = [vp, _ip, _dp]
     L.icp_centroid.argtypes = [vp, _dp, _dp]
     L.icp_find_alignment.argtypes = [vp, _dp, _dp, _dp, _dp]
@@ -168,6 +171,13 @@ class Context:
 
     def reset_scene(self):
         _ck(self._L.icp_reset_scene(self._h))
+
+    def set_nn_mode(self, mode):
+        """'brute' (default, north_star) or 'tree' (exact bounding-box hierarchy); same results."""
+        _ck(self._L.icp_set_nn_mode(self._h, {"brute": 0, "tree": 1}[mode]))
+
+    def nn_mode(self):
+        return ("brute", "tree")[self._L.icp_get_nn_mode(self._h)]
 
     def get_scene(self):
         out = np.empty((self.np, 3))

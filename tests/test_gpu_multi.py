@@ -39,13 +39,16 @@ def test_peer_mailbox_self_exchange(clouds, monkeypatch, align):
     plain.close()
 
 
-def test_two_gpu_sharded_parity():
+@pytest.mark.parametrize("nn", ["brute", "tree"])
+def test_two_gpu_sharded_parity(nn):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, ICP_NN=nn)
     for case in ("cow_tr1", "horse_tr2"):
         r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                             "--master-addr", "127.0.0.1", "--master-port", "29533",
-                            os.path.join(ROOT, "tools", "dist_check.py"), case], capture_output=True, text=True, timeout=600)
+                            os.path.join(ROOT, "tools", "dist_check.py"), case], capture_output=True, text=True, timeout=600,
+                           env=env)
         assert r.returncode == 0, r.stdout + r.stderr
         assert "FAILED" not in r.stdout
