@@ -312,7 +312,7 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         pass
     cpu = None
-    if world == 1:      # the CPU baseline is reported at N = 1 only
+    if world == 1 and not args.skip_cpu_baseline:      # the CPU baseline is reported at N = 1 only
         cpu_iters = 8 if len(m) * len(p) < 5e9 else 1
         pc = p if len(m) * len(p) < 1e11 else p[:4096]
         cv, cit, cdt, cores = cpu_port_throughput(m, pc, cpu_iters, threads=host_threads())
@@ -422,6 +422,7 @@ def main():
     ap.add_argument("--nn", default="brute", choices=["brute", "tree"],
                     help="brute: the exact brute-force search BASELINE.json's metric is quoted on (default); tree: the exact "
                          "bounding-box-hierarchy search (SURVEY 8f-4) - same results, `value` then counts brute-force-EQUIVALENT pairs")
+    ap.add_argument("--skip-cpu-baseline", action="store_true", help="side runs only: leave cpu_baseline null (saves 10-30 s)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank holds a full copy of the scene as its shard (per-GPU work fixed); "
                          "strong = the one scene is cut into N contiguous blocks")

@@ -288,6 +288,23 @@ __global__ void wtree_level_kernel(const float* __restrict__ lower, int n_upper,
     for (int c = 0; c < 3; ++c) { o[c * 32] = lo[c]; o[(3 + c) * 32] = hi[c]; }
 }
 
+// acceptance threshold from the running surrogate minimum (see the header): rounded up, monotone in best2
+__device__ __forceinline__ float tree_thr2(float best2, float twoE)
+{
+    const float r = __fmul_ru(__fsqrt_ru(best2), 1.0000002f);             // (1 + 3u) < 1.0000002
+    const float a = __fadd_ru(r, twoE);
+    return __fmul_ru(__fmul_ru(a, a), 1.000001f);                         // (1 + 16u)
+}
+
+// FP64 value of the reference for (scene point j, model point kk); the scene point is re-read (rare path,
+// keeps three doubles out of the registers of the search loop)
+__device__ __forceinline__ double tree_ref_value(const double* __restrict__ p64x, const double* __restrict__ p64y,
+                                              const double* __restrict__ p64z, int j, const double* __restrict__ m64x,
+                                              const double* __restrict__ m64y, const double* __restrict__ m64z, int kk)
+{
+    return __dsqrt_rn(ref_dist2(p64x[j], p64y[j], p64z[j], m64x[kk], m64y[kk], m64z[kk]));
+}
+
 __global__ void __launch_bounds__(WT_WARPS * 32)
 nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __restrict__ pts,
                 const float4* __restrict__ mhat, const double* __restrict__ m64x, const double* __restrict__ m64y,
@@ -303,42 +320,39 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     if (j >= np) return;                                    // warp-uniform
     constexpr unsigned FULL = 0xffffffffu;
 
-    TreeQuery q;                                            // warp-uniform except (v, k), which are per lane
-    q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
-    q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
-    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    // warp-uniform: the scene point, its error radius, the running surrogate minimum and threshold
+    const float px = phx[j], py = phy[j], pz = phz[j];
+    float twoE;
     {
         const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
-        const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
-        q.twoE = __fadd_ru(__fmul_ru(1.1920932e-7f, __fadd_ru(H, Rm)), 1.0e-30f);
+        const float H = __fsqrt_ru(__fmaf_ru(pz, pz, __fmaf_ru(py, py, __fmul_ru(px, px))));
+        twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
     }
-    q.best2 = q.thr2 = 3.4028235e38f;
-    q.v = __longlong_as_double(0x7ff0000000000000LL);
-    q.k = 0x7fffffff;
+    float best2 = 3.4028235e38f, thr2 = 3.4028235e38f;      // FLT_MAX: empty boxes (+inf) stay above it
+    // per lane: the reference minimum (v, k) over the candidates this lane evaluated
+    double v = __longlong_as_double(0x7ff0000000000000LL);
+    int k = 0x7fffffff;
     if (use_prev) {
         const int kp = idx[j];
         if (kp >= 0 && kp < nm) {
             const float4 m = mhat[kp];
-            const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
-            q.set_best(d2);
-            if (lane == 0) {
-                q.v = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kp], m64y[kp], m64z[kp]));
-                q.k = kp;
-            }
+            best2 = surrogate_direct(px, py, pz, m.x, m.y, m.z);
+            thr2 = tree_thr2(best2, twoE);
+            if (lane == 0) { v = tree_ref_value(p64x, p64y, p64z, j, m64x, m64y, m64z, kp); k = kp; }
         }
     }
 
     // cursor of level l in lane l: block index at that level, children not yet opened
-    const long long my_off = lane < lv.T ? lv.off[lane] : 0;
+    const unsigned my_off = lane < lv.T ? (unsigned)(lv.off[lane] / 192) : 0u;      // in blocks of 192 floats
     int my_node = 0;
     unsigned my_mask = FULL;
     int lvl = lv.T - 1;
     for (;;) {
         const int b = __shfl_sync(FULL, my_node, lvl);
         const unsigned msk = __shfl_sync(FULL, my_mask, lvl);
-        const float* blk = boxes + __shfl_sync(FULL, my_off, lvl) + (size_t)b * 192 + lane;
-        const float d = box_dist2_rd(q.px, q.py, q.pz, blk[0], blk[32], blk[64], blk[96], blk[128], blk[160]);
-        const unsigned alive = __ballot_sync(FULL, d <= q.thr2) & msk;
+        const float* blk = boxes + ((size_t)__shfl_sync(FULL, my_off, lvl) + (size_t)b) * 192 + lane;
+        const float d = box_dist2_rd(px, py, pz, blk[0], blk[32], blk[64], blk[96], blk[128], blk[160]);
+        const unsigned alive = __ballot_sync(FULL, d <= thr2) & msk;
         if (alive == 0u) {
             if (++lvl >= lv.T) break;
             continue;
@@ -358,20 +372,18 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
             const unsigned key = ((rem >> lane) & 1u) ? ((__float_as_uint(d) & ~31u) | (unsigned)lane) : 0xffffffffu;
             const int c = (int)(__reduce_min_sync(FULL, key) & 31u);
             const float4 m = pts[((size_t)b * 32 + c) * 32 + lane];
-            const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
+            const float d2 = surrogate_direct(px, py, pz, m.x, m.y, m.z);
             const float dmin = __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(d2)));   // d2 >= 0: bits are monotone
-            if (dmin < q.best2) q.set_best(dmin);
-            if (d2 <= q.thr2) {
+            if (dmin < best2) { best2 = dmin; thr2 = tree_thr2(dmin, twoE); }
+            if (d2 <= thr2) {
                 const int kk = __float_as_int(m.w);
-                const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
-                if (vv < q.v || (vv == q.v && kk < q.k)) { q.v = vv; q.k = kk; }
+                const double vv = tree_ref_value(p64x, p64y, p64z, j, m64x, m64y, m64z, kk);
+                if (vv < v || (vv == v && kk < k)) { v = vv; k = kk; }
             }
-            rem &= ~(1u << c) & __ballot_sync(FULL, d <= q.thr2);
+            rem &= ~(1u << c) & __ballot_sync(FULL, d <= thr2);
         }
         if (++lvl >= lv.T) break;
     }
-    double v = q.v;
-    int k = q.k;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const double ov = __shfl_xor_sync(FULL, v, o);
@@ -381,7 +393,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     if (k == 0x7fffffff) {       // FP32 surrogate overflowed (scene point > 1e19 away): FP64 scan, first minimum
         v = __longlong_as_double(0x7ff0000000000000LL);
         for (int kk = lane; kk < nm; kk += 32) {
-            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+            const double vv = tree_ref_value(p64x, p64y, p64z, j, m64x, m64y, m64z, kk);
             if (vv < v) { v = vv; k = kk; }
         }
 #pragma unroll
