@@ -119,49 +119,31 @@ __device__ __forceinline__ float box_dist2_rd(float px, float py, float pz, floa
     return __fmaf_rd(ez, ez, __fmaf_rd(ey, ey, __fmul_rd(ex, ex)));
 }
 
-// Running minimum of the reference's value v = sqrt(s) with the lowest index on ties, fed with the squared sums s in
-// ANY order, without a square root per candidate: sqrt is monotone and correctly rounded, so s_new < s(1 - 2^-48)
-// implies sqrt(s_new) < sqrt(s) strictly (the real roots are > 4 ulps apart) and s_new > s(1 + 2^-48) implies the
-// opposite; only inside that band (practically never) are both roots evaluated and compared with the tie rule.
-struct RefBest {
-    double s;
+struct TreeQuery {
+    float px, py, pz;        // p^
+    double qx, qy, qz;       // p (FP64 master)
+    float twoE;              // 2E, rounded up
+    float best2, thr2;       // running surrogate minimum and acceptance threshold
+    double v;                // running reference minimum (v, k), lexicographic
     int k;
-    __device__ __forceinline__ void init() { s = __longlong_as_double(0x7ff0000000000000LL); k = 0x7fffffff; }
-    __device__ __forceinline__ void feed(double sn, int kn)
+    const double *m64x, *m64y, *m64z;
+
+    __device__ __forceinline__ void set_best(float b2)
     {
-        constexpr double EPS = 3.5527136788005009e-15;     // 2^-48
-        if (sn < s * (1.0 - EPS)) { s = sn; k = kn; }
-        else if (sn <= s * (1.0 + EPS)) {
-            const double vn = __dsqrt_rn(sn), vc = __dsqrt_rn(s);
-            if (vn < vc || (vn == vc && kn < k)) { s = sn; k = kn; }
+        best2 = b2;
+        const float r = __fmul_ru(__fsqrt_ru(b2), 1.0000002f);            // (1 + 3u) < 1.0000002
+        const float a = __fadd_ru(r, twoE);
+        thr2 = __fmul_ru(__fmul_ru(a, a), 1.000001f);                     // (1 + 16u) < 1.000001
+    }
+    __device__ __forceinline__ void offer(float d2, int kk)
+    {
+        if (d2 <= thr2) {
+            if (d2 < best2) set_best(d2);
+            const double vv = __dsqrt_rn(ref_dist2(qx, qy, qz, m64x[kk], m64y[kk], m64z[kk]));
+            if (vv < v || (vv == v && kk < k)) { v = vv; k = kk; }
         }
     }
 };
-
-// acceptance threshold from the running surrogate minimum (see the header): rounded up, monotone in best2
-__device__ __forceinline__ float tree_thr2(float best2, float twoE)
-{
-    const float r = __fmul_ru(__fsqrt_ru(best2), 1.0000002f);             // (1 + 3u) < 1.0000002
-    const float a = __fadd_ru(r, twoE);
-    return __fmul_ru(__fmul_ru(a, a), 1.000001f);                         // (1 + 16u)
-}
-
-// 2E = 2 u (1+3u) (|p^| + Rm), rounded up, plus an absolute floor against underflow
-__device__ __forceinline__ float tree_two_e(float px, float py, float pz, const double* __restrict__ geo)
-{
-    const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
-    const float H = __fsqrt_ru(__fmaf_ru(pz, pz, __fmaf_ru(py, py, __fmul_ru(px, px))));
-    return __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
-}
-
-// squared sum of the reference for (scene point j, model point kk); the scene point is re-read (rare path, keeps
-// three doubles out of the registers of the search loop)
-__device__ __forceinline__ double tree_ref_s(const double* __restrict__ p64x, const double* __restrict__ p64y,
-                                             const double* __restrict__ p64z, int j, const double* __restrict__ m64x,
-                                             const double* __restrict__ m64y, const double* __restrict__ m64z, int kk)
-{
-    return ref_dist2(p64x[j], p64y[j], p64z[j], m64x[kk], m64y[kk], m64z[kk]);
-}
 
 __device__ __forceinline__ float surrogate_direct(float px, float py, float pz, float mx, float my, float mz)
 {
@@ -170,10 +152,12 @@ __device__ __forceinline__ float surrogate_direct(float px, float py, float pz, 
 }
 
 // One thread per scene point, near child first, far child on a small local stack; a descend-loop nested in a
-// pop-loop (in a complete binary tree all lanes of a warp reach their leaves together).  Measured alternatives,
-// both slower (profiles/r01h_tree.md): a flat one-node-per-trip loop (+15 %), and per-warp pools of scene points
-// with idle lanes refilled on the fly (ncu shows 10.3 of 32 lanes active on average, but the kernel is bound by
-// the latency of dependent loads, and fewer, longer-lived warps hide less of it: +10 % to 6x).
+// pop-loop (in a complete binary tree all lanes of a warp reach their leaves together).  This plain form is the
+// fastest of those measured A/B on one box (profiles/r01h_tree.md): a flat one-node-per-trip loop +15 %; per-warp
+// pools of scene points with idle lanes refilled on the fly +10 % to 6x (ncu shows 10.3 of 32 lanes active, but the
+// kernel is bound by the latency of dependent loads and fewer, longer-lived warps hide less of it); the leaf
+// scanned branch-free with a compact candidate loop and a square-root-free candidate merge +4..11 % (48 instead of
+// 40 registers: 40 instead of 48 resident warps per SM).
 __global__ void __launch_bounds__(TREE_THREADS)
 nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, int n_leaves /* power of two */,
                const float4* __restrict__ mhat, const double* __restrict__ m64x, const double* __restrict__ m64y,
@@ -187,74 +171,76 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
     const int j = blockIdx.x * TREE_THREADS + threadIdx.x;
     if (j >= np) return;
 
-    const float px = phx[j], py = phy[j], pz = phz[j];
-    const float twoE = tree_two_e(px, py, pz, geo);
-    float best2 = 3.4028235e38f, thr2 = 3.4028235e38f;     // FLT_MAX, not +inf: the empty boxes of padded leaves (+inf) stay above it
-    RefBest rb;
-    rb.init();
+    TreeQuery q;
+    q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
+    q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
+    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    {
+        const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
+        const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
+        // 2E = 2 u (1+3u) (|p^| + Rm), plus an absolute floor against underflow
+        q.twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
+    }
+    q.best2 = q.thr2 = 3.4028235e38f;     // FLT_MAX, not +inf: the empty boxes of padded leaves (+inf) stay above it
+    q.v = __longlong_as_double(0x7ff0000000000000LL);
+    q.k = 0x7fffffff;
     if (use_prev) {      // last iteration's match: a near-optimal bound before the first node is opened
         const int kp = idx[j];
         if (kp >= 0 && kp < nm) {
             const float4 m = mhat[kp];
-            best2 = surrogate_direct(px, py, pz, m.x, m.y, m.z);
-            thr2 = tree_thr2(best2, twoE);
-            rb.feed(tree_ref_s(p64x, p64y, p64z, j, m64x, m64y, m64z, kp), kp);
+            q.offer(surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z), kp);
         }
     }
 
     int st_node[TREE_STACK];
     float st_d[TREE_STACK];
-    int sp = 0, node = 1;
+    int sp = 0;
+    int node = 1;
+    float nd = 0.0f;
     const float4* nodes4 = reinterpret_cast<const float4*>(nodes);
     for (;;) {
-        while (node < n_leaves) {                                     // internal: open both children, near one first
-            const float4 a = nodes4[(size_t)node * 3], b = nodes4[(size_t)node * 3 + 1],
-                         c = nodes4[(size_t)node * 3 + 2];            // children 2*node, 2*node+1 = 12 floats
-            const float d0 = box_dist2_rd(px, py, pz, a.x, a.y, a.z, a.w, b.x, b.y);
-            const float d1 = box_dist2_rd(px, py, pz, b.z, b.w, c.x, c.y, c.z, c.w);
-            const bool first0 = d0 <= d1;
-            const float dn = first0 ? d0 : d1, df = first0 ? d1 : d0;
-            if (df <= thr2) {            // one push per level at most: sp <= log2(n_leaves) < TREE_STACK
-                st_node[sp] = 2 * node + (first0 ? 1 : 0);
-                st_d[sp] = df;
-                ++sp;
+        if (nd <= q.thr2) {
+            while (node < n_leaves) {                                 // internal: open both children, near one first
+                const float4 a = nodes4[(size_t)node * 3], b = nodes4[(size_t)node * 3 + 1],
+                             c = nodes4[(size_t)node * 3 + 2];        // children 2*node, 2*node+1 = 12 floats
+                const float d0 = box_dist2_rd(q.px, q.py, q.pz, a.x, a.y, a.z, a.w, b.x, b.y);
+                const float d1 = box_dist2_rd(q.px, q.py, q.pz, b.z, b.w, c.x, c.y, c.z, c.w);
+                const bool first0 = d0 <= d1;
+                const float dn = first0 ? d0 : d1, df = first0 ? d1 : d0;
+                const int near = 2 * node + (first0 ? 0 : 1), far = 2 * node + (first0 ? 1 : 0);
+                if (df <= q.thr2) {      // one push per level at most: sp <= log2(n_leaves) < TREE_STACK
+                    st_node[sp] = far; st_d[sp] = df; ++sp; }
+                node = near;
+                nd = dn;
+                if (!(dn <= q.thr2)) { node = -1; break; }
             }
-            node = 2 * node + (first0 ? 0 : 1);
-            if (!(dn <= thr2)) { node = -1; break; }
-        }
-        if (node >= n_leaves) {
-            const float4* lp = pts + (size_t)(node - n_leaves) * TREE_LEAF;
+            if (node >= n_leaves) {
+                const float4* lp = pts + (size_t)(node - n_leaves) * TREE_LEAF;
 #pragma unroll
-            for (int i = 0; i < TREE_LEAF; ++i) {
-                const float4 m = lp[i];
-                const float d2 = surrogate_direct(px, py, pz, m.x, m.y, m.z);
-                if (d2 <= thr2) {
-                    if (d2 < best2) { best2 = d2; thr2 = tree_thr2(d2, twoE); }
-                    const int kk = __float_as_int(m.w);
-                    rb.feed(tree_ref_s(p64x, p64y, p64z, j, m64x, m64y, m64z, kk), kk);
+                for (int i = 0; i < TREE_LEAF; ++i) {
+                    const float4 m = lp[i];
+                    q.offer(surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z), __float_as_int(m.w));
                 }
             }
         }
-        node = -1;
-        while (sp > 0) {                                              // next node that still beats the threshold
-            --sp;
-            if (st_d[sp] <= thr2) { node = st_node[sp]; break; }
-        }
-        if (node < 0) break;
+        if (sp == 0) break;
+        --sp;
+        node = st_node[sp];
+        nd = st_d[sp];
     }
-    int k = rb.k;
-    if (k == 0x7fffffff) {
+    if (q.k == 0x7fffffff) {
         // nothing was accepted: the FP32 surrogate overflowed (a scene point > 1e19 away from the model).  Plain
         // FP64 scan in index order with the reference's expression, first minimum.
         double bv = __longlong_as_double(0x7ff0000000000000LL);
-        k = 0;
+        q.k = 0;
         for (int kk = 0; kk < nm; ++kk) {
-            const double vv = __dsqrt_rn(tree_ref_s(p64x, p64y, p64z, j, m64x, m64y, m64z, kk));
-            if (vv < bv) { bv = vv; k = kk; }
+            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+            if (vv < bv) { bv = vv; q.k = kk; }
         }
     }
-    idx[j] = k;
+    idx[j] = q.k;
 }
+
 
 // ------------------------------------------------------------------------------------------------
 // Wide form: 32-ary hierarchy, ONE WARP PER SCENE POINT.  Leaf = 32 consecutive Morton-sorted model points
@@ -263,6 +249,8 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
 // one path (no divergence), the tree is 3 levels deep for horse and 4 for 2^22 points, and the per-level
 // cursor (node, remaining-children mask) lives in the registers of lane `level` — there is no stack in memory.
 // Same bound, same acceptance rule and same FP64 decision as the thread-per-point kernel above.
+// Measured and rejected here too: 32 registers / 8 CTAs per SM (+8 %: the kernel is issue bound, not occupancy
+// bound), a square-root-free candidate merge with the scene point re-read per candidate (+4 %).
 constexpr int WT_WARPS = 8;     // scene points per CTA
 
 __global__ void wtree_leaf_boxes_kernel(const float4* __restrict__ pts, int n_leaves, int n_padded,
@@ -324,37 +312,42 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     if (j >= np) return;                                    // warp-uniform
     constexpr unsigned FULL = 0xffffffffu;
 
-    // warp-uniform: the scene point, its error radius, the running surrogate minimum and threshold
-    const float px = phx[j], py = phy[j], pz = phz[j];
-    const float twoE = tree_two_e(px, py, pz, geo);
-    float best2 = 3.4028235e38f, thr2 = 3.4028235e38f;      // FLT_MAX: empty boxes (+inf) stay above it
-    RefBest rb;                                             // per lane: minimum over the candidates this lane evaluated
-    rb.init();
+    TreeQuery q;                                            // warp-uniform except (v, k), which are per lane
+    q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
+    q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
+    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    {
+        const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
+        const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
+        q.twoE = __fadd_ru(__fmul_ru(1.1920932e-7f, __fadd_ru(H, Rm)), 1.0e-30f);
+    }
+    q.best2 = q.thr2 = 3.4028235e38f;
+    q.v = __longlong_as_double(0x7ff0000000000000LL);
+    q.k = 0x7fffffff;
     if (use_prev) {
         const int kp = idx[j];
         if (kp >= 0 && kp < nm) {
             const float4 m = mhat[kp];
-            best2 = surrogate_direct(px, py, pz, m.x, m.y, m.z);
-            thr2 = tree_thr2(best2, twoE);
-            if (lane == 0) rb.feed(tree_ref_s(p64x, p64y, p64z, j, m64x, m64y, m64z, kp), kp);
+            const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
+            q.set_best(d2);
+            if (lane == 0) {
+                q.v = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kp], m64y[kp], m64z[kp]));
+                q.k = kp;
+            }
         }
     }
 
     // cursor of level l in lane l: block index at that level, children not yet opened
-    const unsigned my_off = lane < lv.T ? (unsigned)(lv.off[lane] / 192) : 0u;      // in blocks of 192 floats
+    const long long my_off = lane < lv.T ? lv.off[lane] : 0;
     int my_node = 0;
     unsigned my_mask = FULL;
     int lvl = lv.T - 1;
     for (;;) {
         const int b = __shfl_sync(FULL, my_node, lvl);
         const unsigned msk = __shfl_sync(FULL, my_mask, lvl);
-        if (msk == 0u) {                                    // every child of this block was opened already
-            if (++lvl >= lv.T) break;
-            continue;
-        }
-        const float* blk = boxes + ((size_t)__shfl_sync(FULL, my_off, lvl) + (size_t)b) * 192 + lane;
-        const float d = box_dist2_rd(px, py, pz, blk[0], blk[32], blk[64], blk[96], blk[128], blk[160]);
-        const unsigned alive = __ballot_sync(FULL, d <= thr2) & msk;
+        const float* blk = boxes + __shfl_sync(FULL, my_off, lvl) + (size_t)b * 192 + lane;
+        const float d = box_dist2_rd(q.px, q.py, q.pz, blk[0], blk[32], blk[64], blk[96], blk[128], blk[160]);
+        const unsigned alive = __ballot_sync(FULL, d <= q.thr2) & msk;
         if (alive == 0u) {
             if (++lvl >= lv.T) break;
             continue;
@@ -374,19 +367,20 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
             const unsigned key = ((rem >> lane) & 1u) ? ((__float_as_uint(d) & ~31u) | (unsigned)lane) : 0xffffffffu;
             const int c = (int)(__reduce_min_sync(FULL, key) & 31u);
             const float4 m = pts[((size_t)b * 32 + c) * 32 + lane];
-            const float d2 = surrogate_direct(px, py, pz, m.x, m.y, m.z);
+            const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
             const float dmin = __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(d2)));   // d2 >= 0: bits are monotone
-            if (dmin < best2) { best2 = dmin; thr2 = tree_thr2(dmin, twoE); }
-            if (d2 <= thr2) {
+            if (dmin < q.best2) q.set_best(dmin);
+            if (d2 <= q.thr2) {
                 const int kk = __float_as_int(m.w);
-                rb.feed(tree_ref_s(p64x, p64y, p64z, j, m64x, m64y, m64z, kk), kk);
+                const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+                if (vv < q.v || (vv == q.v && kk < q.k)) { q.v = vv; q.k = kk; }
             }
-            rem &= ~(1u << c) & __ballot_sync(FULL, d <= thr2);
+            rem &= ~(1u << c) & __ballot_sync(FULL, d <= q.thr2);
         }
         if (++lvl >= lv.T) break;
     }
-    double v = __dsqrt_rn(rb.s);                            // one root per lane, then (v, lowest index) over the warp
-    int k = rb.k;
+    double v = q.v;
+    int k = q.k;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const double ov = __shfl_xor_sync(FULL, v, o);
@@ -396,7 +390,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     if (k == 0x7fffffff) {       // FP32 surrogate overflowed (scene point > 1e19 away): FP64 scan, first minimum
         v = __longlong_as_double(0x7ff0000000000000LL);
         for (int kk = lane; kk < nm; kk += 32) {
-            const double vv = __dsqrt_rn(tree_ref_s(p64x, p64y, p64z, j, m64x, m64y, m64z, kk));
+            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
             if (vv < v) { v = vv; k = kk; }
         }
 #pragma unroll

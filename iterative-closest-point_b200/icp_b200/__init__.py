@@ -63,7 +63,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None:
         return _lib
-    path = path or LIB_PATH
+    path = path or os.environ.get("ICP_B200_LIB") or LIB_PATH      # ICP_B200_LIB: A/B runs of two builds
     if not os.path.exists(path):
         raise ImportError(f"{path} is missing: build it with `make -C {os.path.dirname(_PKG)}` "
                           "(there is no CPU fallback)")
