@@ -25,7 +25,7 @@ KEEP = ("gpu__time_duration.sum", "launch__registers_per_thread", "launch__occup
         "sm__pipe_alu_cycles_active.avg", "sm__inst_executed_pipe_lsu.avg", "sm__inst_executed_pipe_fp64.avg",
         "sm__pipe_fp64_cycles_active.avg", "sm__pipe_tensor", "sm__inst_issued.avg", "sm__issue_active.avg",
         "smsp__issue_active.avg", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg",
-        "gpu__dram_throughput.avg", "lts__t_bytes.sum", "lts__t_sector_hit_rate", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        "gpu__dram_throughput.avg", "lts__t_bytes.sum", "lts__t_sector_hit_rate", "l1tex__t_sector_hit_rate", "l1tex__throughput.avg", "lts__throughput.avg", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
         "smsp__inst_executed.sum", "sm__cycles_elapsed.avg", "smsp__cycles_active.avg", "sm__throughput.avg",
         "smsp__average_warps_issue_stalled", "smsp__thread_inst_executed_per_inst_executed",
         "sm__sass_thread_inst_executed_op_ffma_pred_on.sum", "sm__sass_thread_inst_executed_op_fadd_pred_on.sum",
