@@ -57,3 +57,16 @@ def test_size_mismatch_exits_like_reference(tmp_path, cloud_dir):
     assert "[error] Point sets need to have the same number of points." in r.stderr
     r = run_icp([ref, scene, "2"], tmp_path, env={"ICP_ALLOW_UNEQUAL": "1"})
     assert r.returncode == 0 and r.stderr.count("[ICP] iteration number") == 2
+
+
+def test_tree_search_driver_writes_the_same_bytes(tmp_path, cloud_dir):
+    # ICP_NN=tree (read by icp_create) changes how the correspondences are found, not what they are: the driver's
+    # stderr lines and output.txt must be byte-identical to the brute-force run
+    ref, scene = cloud_text_path("cow_ref", cloud_dir), cloud_text_path("cow_tr1", cloud_dir)
+    (tmp_path / "a").mkdir()
+    (tmp_path / "b").mkdir()
+    ra = run_icp([ref, scene, "10"], tmp_path / "a")
+    rb = run_icp([ref, scene, "10"], tmp_path / "b", env={"ICP_NN": "tree"})
+    assert ra.returncode == rb.returncode == 0
+    assert ra.stderr == rb.stderr and ra.stdout == rb.stdout
+    assert (tmp_path / "a" / "output.txt").read_bytes() == (tmp_path / "b" / "output.txt").read_bytes()
