@@ -101,7 +101,7 @@ struct icp_ctx {
     // exact tree search, opt-in: ICP_NN=tree / icp_set_nn_mode
     int nn_mode = ICP_NN_BRUTE;
     TreeDev tree;
-    bool tree_built = false;
+    bool tree_built[2] = {false, false};   // [0] binary form, [1] wide form: built on first use, for the model currently set
     int tree_form = 0;                     // ICP_TREE: 0 auto, 1 wide (warp per point, 32-ary), 2 binary (thread per point)
     double h_Rm = 0.0;                     // geo[3] of the current model (the tree needs 1e-12 <= Rm <= 1e12)
     int32_t* d_idx_out = nullptr; size_t idx_out_cap = 0;
@@ -162,32 +162,37 @@ bool tree_active(const icp_ctx* c)
     return c->nn_mode == ICP_NN_TREE && (c->h_Rm == 0.0 || (c->h_Rm >= 1e-12 && c->h_Rm <= 1e12));
 }
 
-// Builds the model's bounding-box hierarchy on first use after icp_set_model (tree mode only).
+// Which form searches the current scene: ICP_TREE forces one; otherwise a warp per point while the scene is small.
+bool tree_use_wide(const icp_ctx* c) { return c->tree_form == 1 || (c->tree_form == 0 && c->s.np <= 131072); }
+
+// Builds the model's bounding-box hierarchy (the form the current scene needs) on first use after icp_set_model.
 int ensure_tree(icp_ctx* c)
 {
-    if (!tree_active(c) || c->tree_built) return ICP_OK;
+    if (!tree_active(c)) return ICP_OK;
+    const bool wide = tree_use_wide(c);
+    if (c->tree_built[wide]) return ICP_OK;
     int r;
     const int64_t leaves = (c->m.nm + TREE_LEAF - 1) / TREE_LEAF;
     int nl = 1;
     while (nl < leaves) nl *= 2;
-    if (c->tree.cap_leaves < (size_t)nl) {
+    if (!wide && c->tree.cap_leaves < (size_t)nl) {
         if ((r = dalloc(&c->tree.nodes, (size_t)nl * 2 * 6)) || (r = dalloc(&c->tree.pts, (size_t)nl * TREE_LEAF))) return r;
         c->tree.cap_leaves = (size_t)nl;
     }
     c->tree.n_leaves = nl;
     const size_t wfloats = wtree_plan(c->m.nm, c->tree.w);
-    if (c->tree.cap_wboxes < wfloats) {
+    if (wide && c->tree.cap_wboxes < wfloats) {
         if ((r = dalloc(&c->tree.wboxes, wfloats))) return r;
         c->tree.cap_wboxes = wfloats;
     }
-    if (c->tree.cap_wpts < (size_t)c->tree.w.count[0] * 32) {
+    if (wide && c->tree.cap_wpts < (size_t)c->tree.w.count[0] * 32) {
         if ((r = dalloc(&c->tree.wpts, (size_t)c->tree.w.count[0] * 32))) return r;
         c->tree.cap_wpts = (size_t)c->tree.w.count[0] * 32;
     }
     if ((r = ensure_sort(c, (size_t)c->m.nm))) return r;
-    const int e = tree_build(c->m, c->tree, c->d_keys, c->d_keys_alt, c->d_vals, c->d_vals_alt, c->d_cub, c->cub_bytes, c->st);
+    const int e = tree_build(c->m, c->tree, wide, c->d_keys, c->d_keys_alt, c->d_vals, c->d_vals_alt, c->d_cub, c->cub_bytes, c->st);
     if (e != 0) { g_err = std::string("tree_build: ") + cudaGetErrorString((cudaError_t)e); return ICP_ERR_CUDA; }
-    c->tree_built = true;
+    c->tree_built[wide] = true;
     return ICP_OK;
 }
 
@@ -245,12 +250,11 @@ void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent
              cudaEvent_t e3 = nullptr)
 {
     if (e0) cudaEventRecord(e0, c->st);
-    if (tree_active(c) && c->tree_built) {
+    if (tree_active(c) && c->tree_built[tree_use_wide(c)]) {
         // measured (profiles/r01h_tree.md): a warp per point wins while the grid is a few waves (cow 0.014 vs 0.052 ms,
         // horse 128 vs 285 us per search: the slowest thread no longer sets the kernel time); a thread per point
         // wins once there are enough points to fill the machine either way (2^18: 0.19 vs 0.47 ms, 2^22: 2x)
-        const bool wide = c->tree_form == 1 || (c->tree_form == 0 && c->s.np <= 131072);
-        if (wide)
+        if (tree_use_wide(c))
             launch_nn_wtree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
         else
             launch_nn_tree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
@@ -460,7 +464,7 @@ int icp_set_model(icp_ctx* c, const double* m_xyz, int64_t nm)
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&c->h_Rm, c->m.geo + 3, sizeof(double), cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
-    c->tree_built = false;
+    c->tree_built[0] = c->tree_built[1] = false;
     c->have_model = true;
     c->have_idx = false;
     c->stats.nm = nm;

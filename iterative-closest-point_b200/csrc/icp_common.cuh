@@ -110,9 +110,9 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                      int sm_count, cudaStream_t st, unsigned long long* trace = nullptr);
 int nn_exact_batch_points();
-// tree search (tree_kernels.cu).  tree_build returns a cudaError_t; use_prev: idx[] holds the previous matches.
+// tree search (tree_kernels.cu).  tree_build builds ONE form (wide or binary) and returns a cudaError_t; use_prev: idx[] holds the previous matches.
 size_t tree_sort_bytes(int n);
-int tree_build(const ModelDev& m, TreeDev& t, uint32_t* keys, uint32_t* keys_alt,
+int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_t* keys_alt,
                int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, cudaStream_t st);
 size_t wtree_plan(int64_t nm, WideLevels& w);
 void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int use_prev, int* ctl, int honor_done,

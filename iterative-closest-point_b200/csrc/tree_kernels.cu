@@ -253,6 +253,83 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
 // bound), a square-root-free candidate merge with the scene point re-read per candidate (+4 %).
 constexpr int WT_WARPS = 8;     // scene points per CTA
 
+// Leaf quality.  32 consecutive points of a Morton order make poor leaves on a surface (the curve jumps): on horse a
+// search had 10.2 leaves inside its final radius.  Re-ordering every block of KD_B consecutive Morton-sorted points by
+// median splits along the widest axis (a k-d order, 6 levels: 2048 -> 32 points) brings that to 4.7 leaves and 4.8 -> 3.9
+// level-0 blocks (CPU emulation on horse, profiles/r01i_tree_order.md) while the coarse levels keep the Morton
+// structure.  One CTA per block, everything in shared memory: per level a bounding box per segment (warp reduction +
+// shared atomics on order-preserving integer keys), then one bitonic sort of ALL segments at once by the coordinate
+// of their own widest axis.  Padding (+inf) sorts to the end of its segment at every level, so the valid points stay a
+// contiguous prefix.
+constexpr int KD_B = 2048;
+constexpr int KD_T = KD_B / 2;
+constexpr int KD_MIN_POINTS = 8192;     // below: the search is launch / latency bound and the ~0.1 ms of this kernel does not pay (cow)
+
+__device__ __forceinline__ int kd_enc(float f)          // order-preserving float -> int
+{
+    const int i = __float_as_int(f);
+    return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float kd_dec(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+__device__ __forceinline__ float kd_comp(const float4& v, int ax) { return ax == 0 ? v.x : (ax == 1 ? v.y : v.z); }
+
+__global__ void __launch_bounds__(KD_T) wtree_local_kd_kernel(float4* __restrict__ pts, int nm)
+{
+    __shared__ float4 P[KD_B];
+    __shared__ int smin[KD_B / 64][3], smax[KD_B / 64][3];
+    __shared__ int axis[KD_B / 64];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int base = blockIdx.x * KD_B;
+    const int valid = nm - base < KD_B ? nm - base : KD_B;
+    for (int e = tid; e < KD_B; e += KD_T)
+        P[e] = e < valid ? pts[base + e] : make_float4(INFINITY, INFINITY, INFINITY, __int_as_float(-1));
+    __syncthreads();
+    for (int S = KD_B; S >= 64; S >>= 1) {
+        const int nseg = KD_B / S;
+        if (tid < nseg * 3) { smin[tid / 3][tid % 3] = 0x7fffffff; smax[tid / 3][tid % 3] = (int)0x80000000; }
+        __syncthreads();
+        for (int e = tid; e < KD_B; e += KD_T) {       // a warp's 32 elements lie in one segment (S >= 64)
+            const float4 v = P[e];
+            float lo[3] = {v.x, v.y, v.z}, hi[3] = {v.x, v.y, v.z};
+            if (e >= valid) { lo[0] = lo[1] = lo[2] = INFINITY; hi[0] = hi[1] = hi[2] = -INFINITY; }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+                    hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+                }
+            if (lane == 0) {
+                const int sg = e / S;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { atomicMin(&smin[sg][c], kd_enc(lo[c])); atomicMax(&smax[sg][c], kd_enc(hi[c])); }
+            }
+        }
+        __syncthreads();
+        if (tid < nseg) {
+            float best = -1.0f;
+            int ax = 0;
+            for (int c = 0; c < 3; ++c) {
+                const float ext = kd_dec(smax[tid][c]) - kd_dec(smin[tid][c]);     // NaN / -inf for an all-padding segment
+                if (ext > best) { best = ext; ax = c; }
+            }
+            axis[tid] = ax;
+        }
+        __syncthreads();
+        for (int k = 2; k <= S; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                const int i = ((tid & ~(j - 1)) << 1) | (tid & (j - 1));           // bit j clear; partner has it set
+                const int ip = i | j;
+                const bool asc = (k == S) || ((i & k) == 0);                       // last merge: every segment ascending
+                const int ax = axis[i / S];
+                const float4 a = P[i], b = P[ip];
+                if ((kd_comp(a, ax) > kd_comp(b, ax)) == asc) { P[i] = b; P[ip] = a; }
+                __syncthreads();
+            }
+    }
+    for (int e = tid; e < valid; e += KD_T) pts[base + e] = P[e];
+}
+
 __global__ void wtree_leaf_boxes_kernel(const float4* __restrict__ pts, int n_leaves, int n_padded,
                                         float* __restrict__ boxes0)
 {
@@ -407,22 +484,27 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
 }  // namespace
 
 // Builds the hierarchy for the model currently in `m` (mhat / geo valid); keys/vals/perm/cub: sort scratch for nm items.
-int tree_build(const ModelDev& m, TreeDev& t, uint32_t* keys, uint32_t* keys_alt,
+int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_t* keys_alt,
                int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, cudaStream_t st)
 {
     const int nm = (int)m.nm;
     tree_keys_kernel<<<(nm + 255) / 256, 256, 0, st>>>(m.mhat, nm, m.geo, keys, vals);
     cudaError_t e = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys_alt, vals, perm, nm, 0, 30, st);
     if (e != cudaSuccess) return (int)e;
+    if (!wide) {
     const int n_slots = t.n_leaves * TREE_LEAF;
     tree_points_kernel<<<(n_slots + 255) / 256, 256, 0, st>>>(m.mhat, perm, nm, n_slots, t.pts);
+    if (nm >= KD_MIN_POINTS) wtree_local_kd_kernel<<<(nm + KD_B - 1) / KD_B, KD_T, 0, st>>>(t.pts, nm);
     tree_leaf_boxes_kernel<<<(t.n_leaves + 255) / 256, 256, 0, st>>>(t.pts, t.n_leaves, (nm + TREE_LEAF - 1) / TREE_LEAF,
                                                                      t.nodes);
     for (int first = t.n_leaves / 2; first >= 1; first /= 2)
         tree_level_kernel<<<(first + 255) / 256, 256, 0, st>>>(t.nodes, first, first);
+    return (int)cudaGetLastError();
+    }
     // wide form (same sorted order)
     const int n0 = t.w.count[0];
     tree_points_kernel<<<(n0 * 32 + 255) / 256, 256, 0, st>>>(m.mhat, perm, nm, n0 * 32, t.wpts);
+    if (nm >= KD_MIN_POINTS) wtree_local_kd_kernel<<<(nm + KD_B - 1) / KD_B, KD_T, 0, st>>>(t.wpts, nm);
     {
         const int padded = (n0 + 31) / 32 * 32;
         wtree_leaf_boxes_kernel<<<(padded * 32 + 255) / 256, 256, 0, st>>>(t.wpts, n0, padded, t.wboxes + t.w.off[0]);
