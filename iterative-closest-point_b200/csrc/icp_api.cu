@@ -190,7 +190,19 @@ int ensure_tree(icp_ctx* c)
         c->tree.cap_wpts = (size_t)c->tree.w.count[0] * 32;
     }
     if ((r = ensure_sort(c, (size_t)c->m.nm))) return r;
-    const int e = tree_build(c->m, c->tree, wide, c->d_keys, c->d_keys_alt, c->d_vals, c->d_vals_alt, c->d_cub, c->cub_bytes, c->st);
+    void* kd = nullptr;
+    if (c->m.nm >= kd_global_min_points()) {
+        const size_t need = kd_scratch_bytes((int)c->m.nm, nullptr);
+        if (c->tree.cap_kd < need) {
+            if (c->tree.kd_scratch) cudaFree(c->tree.kd_scratch);
+            c->tree.kd_scratch = nullptr;
+            c->tree.cap_kd = 0;
+            CK(cudaMalloc(&c->tree.kd_scratch, need));
+            c->tree.cap_kd = need;
+        }
+        kd = c->tree.kd_scratch;
+    }
+    const int e = tree_build(c->m, c->tree, wide, c->d_keys, c->d_keys_alt, c->d_vals, c->d_vals_alt, c->d_cub, c->cub_bytes, kd, c->st);
     if (e != 0) { g_err = std::string("tree_build: ") + cudaGetErrorString((cudaError_t)e); return ICP_ERR_CUDA; }
     c->tree_built[wide] = true;
     return ICP_OK;
@@ -435,6 +447,7 @@ void icp_destroy(icp_ctx* c)
     dfree(c->d_stage); dfree(c->d_partials); dfree(c->d_mom); dfree(c->d_xf); dfree(c->d_err_sum); dfree(c->d_out6);
     dfree(c->d_err_hist); dfree(c->d_ctl); dfree(c->d_keys); dfree(c->d_keys_alt); dfree(c->d_vals);
     dfree(c->d_idx_out); dfree(c->d_vals_alt); dfree(c->tree.nodes); dfree(c->tree.pts); dfree(c->tree.wboxes); dfree(c->tree.wpts);
+    if (c->tree.kd_scratch) cudaFree(c->tree.kd_scratch);
     if (c->d_cub) cudaFree(c->d_cub);
     for (auto e : c->ev_filter) cudaEventDestroy(e);
     if (c->ev0) cudaEventDestroy(c->ev0);

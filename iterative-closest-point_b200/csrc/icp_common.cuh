@@ -98,6 +98,8 @@ struct TreeDev {
     float* wboxes = nullptr;     // all levels of the wide form
     float4* wpts = nullptr;      // [count[0] * 32] sorted points, padded with the last one
     size_t cap_wboxes = 0, cap_wpts = 0;
+    void* kd_scratch = nullptr;  // global k-d levels of large models (tree_build)
+    size_t cap_kd = 0;
 };
 
 // ---- launchers (defined in nn_kernels.cu / align_kernels.cu) ------------------------------------
@@ -113,7 +115,9 @@ int nn_exact_batch_points();
 // tree search (tree_kernels.cu).  tree_build builds ONE form (wide or binary) and returns a cudaError_t; use_prev: idx[] holds the previous matches.
 size_t tree_sort_bytes(int n);
 int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_t* keys_alt,
-               int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, cudaStream_t st);
+               int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, void* kd_scratch /* nullable */, cudaStream_t st);
+size_t kd_scratch_bytes(int nm, size_t* cub_bytes_out);
+int kd_global_min_points();
 size_t wtree_plan(int64_t nm, WideLevels& w);
 void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int use_prev, int* ctl, int honor_done,
                      cudaStream_t st, int* progress = nullptr);

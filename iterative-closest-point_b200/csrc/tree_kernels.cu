@@ -330,6 +330,81 @@ __global__ void __launch_bounds__(KD_T) wtree_local_kd_kernel(float4* __restrict
     for (int e = tid; e < valid; e += KD_T) pts[base + e] = P[e];
 }
 
+// The same median splits ABOVE the 2048-point blocks, for large models (CPU emulation, 2^17 uniform points, binary form:
+// 35 boxes inside the final radius with local splits only, 22 with 4 more levels, 20 with a k-d order from the top).
+// A level = bounding box per segment (block reduction + atomics on order-preserving keys), widest axis, one radix
+// sort of (segment, coordinate) keys, one gather.  Segments are equal-sized and aligned, so the segment of an element
+// is its index / S and nothing but the order changes.
+constexpr int KD_GLOBAL_LEVELS = 4;
+constexpr int KD_GLOBAL_MIN_POINTS = 131072;
+
+__global__ void kd_fill_kernel(int* __restrict__ smin, int* __restrict__ smax, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { smin[i] = 0x7fffffff; smax[i] = (int)0x80000000; }
+}
+
+__global__ void __launch_bounds__(256) kd_seg_bbox_kernel(const float4* __restrict__ pts, int nm, int S,
+                                                          int* __restrict__ smin, int* __restrict__ smax)
+{
+    __shared__ float red[6][8];
+    const int i = blockIdx.x * 256 + threadIdx.x;           // S is a multiple of 256: one segment per block
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (i < nm) {
+        const float4 v = pts[i];
+        lo[0] = hi[0] = v.x; lo[1] = hi[1] = v.y; lo[2] = hi[2] = v.z;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+            hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+        }
+    if ((threadIdx.x & 31) == 0)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { red[c][threadIdx.x >> 5] = lo[c]; red[3 + c][threadIdx.x >> 5] = hi[c]; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float a = INFINITY, b = -INFINITY;
+        for (int w = 0; w < 8; ++w) { a = fminf(a, red[threadIdx.x][w]); b = fmaxf(b, red[3 + threadIdx.x][w]); }
+        const int sg = (blockIdx.x * 256) / S;
+        atomicMin(&smin[sg * 3 + threadIdx.x], kd_enc(a));
+        atomicMax(&smax[sg * 3 + threadIdx.x], kd_enc(b));
+    }
+}
+
+__global__ void kd_seg_axis_kernel(const int* __restrict__ smin, const int* __restrict__ smax, int nseg, int* __restrict__ axis)
+{
+    const int sg = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sg >= nseg) return;
+    float best = -1.0f;
+    int ax = 0;
+    for (int c = 0; c < 3; ++c) {
+        const float ext = kd_dec(smax[sg * 3 + c]) - kd_dec(smin[sg * 3 + c]);
+        if (ext > best) { best = ext; ax = c; }
+    }
+    axis[sg] = ax;
+}
+
+__global__ void kd_keys_kernel(const float4* __restrict__ pts, int nm, int S, const int* __restrict__ axis,
+                               unsigned long long* __restrict__ keys, int32_t* __restrict__ vals)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nm) return;
+    const int sg = i / S;
+    unsigned u = __float_as_uint(kd_comp(pts[i], axis[sg]));
+    u ^= (u >> 31) ? 0xffffffffu : 0x80000000u;             // order-preserving float -> unsigned
+    keys[i] = ((unsigned long long)sg << 32) | u;
+    vals[i] = i;
+}
+
+__global__ void kd_gather_kernel(const float4* __restrict__ src, const int32_t* __restrict__ vals, int nm, float4* __restrict__ dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nm) dst[i] = src[vals[i]];
+}
+
 __global__ void wtree_leaf_boxes_kernel(const float4* __restrict__ pts, int n_leaves, int n_padded,
                                         float* __restrict__ boxes0)
 {
@@ -483,9 +558,60 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
 
 }  // namespace
 
+// Scratch of the global k-d levels for nm points: two key arrays, two value arrays, one point array, segment tables,
+// the radix sort's temporary.
+size_t kd_scratch_bytes(int nm, size_t* cub_bytes_out)
+{
+    size_t cub_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                    (int32_t*)nullptr, (int32_t*)nullptr, nm, 0, 64, (cudaStream_t)0);
+    if (cub_bytes_out) *cub_bytes_out = cub_bytes;
+    const size_t n = ((size_t)nm + 255) / 256 * 256;
+    return n * (2 * 8 + 2 * 4 + 16) + 3 * 4 * 7 * (n / KD_B + 2) + cub_bytes + 1024;
+}
+
+// pts[0, nm): Morton order in, k-d order of the top KD_GLOBAL_LEVELS levels out (in place; `scratch` as sized above)
+static cudaError_t kd_global_levels(float4* pts, int nm, void* scratch, cudaStream_t st)
+{
+    size_t cub_bytes = 0;
+    kd_scratch_bytes(nm, &cub_bytes);
+    const size_t n = ((size_t)nm + 255) / 256 * 256;
+    char* p = static_cast<char*>(scratch);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(p); p += n * 8;
+    unsigned long long* keys_alt = reinterpret_cast<unsigned long long*>(p); p += n * 8;
+    float4* alt = reinterpret_cast<float4*>(p); p += n * 16;
+    int32_t* vals = reinterpret_cast<int32_t*>(p); p += n * 4;
+    int32_t* vals_alt = reinterpret_cast<int32_t*>(p); p += n * 4;
+    const size_t seg_cap = 7 * (n / KD_B + 2);
+    int* smin = reinterpret_cast<int*>(p); p += seg_cap * 4;
+    int* smax = reinterpret_cast<int*>(p); p += seg_cap * 4;
+    int* axis = reinterpret_cast<int*>(p); p += seg_cap * 4;
+    p += (256 - (reinterpret_cast<uintptr_t>(p) & 255)) & 255;      // the sort's temporary wants cudaMalloc-like alignment
+    void* cub_tmp = p;
+    float4 *src = pts, *dst = alt;
+    for (int g = 0; g < KD_GLOBAL_LEVELS; ++g) {
+        const int S = KD_B << (KD_GLOBAL_LEVELS - g);           // 32768, 16384, 8192, 4096
+        const int nseg = (nm + S - 1) / S;
+        int seg_bits = 1;
+        while ((1 << seg_bits) < nseg) ++seg_bits;
+        kd_fill_kernel<<<(nseg * 3 + 255) / 256, 256, 0, st>>>(smin, smax, nseg * 3);
+        kd_seg_bbox_kernel<<<(nm + 255) / 256, 256, 0, st>>>(src, nm, S, smin, smax);
+        kd_seg_axis_kernel<<<(nseg + 255) / 256, 256, 0, st>>>(smin, smax, nseg, axis);
+        kd_keys_kernel<<<(nm + 255) / 256, 256, 0, st>>>(src, nm, S, axis, keys, vals);
+        size_t bytes = cub_bytes;
+        const cudaError_t e = cub::DeviceRadixSort::SortPairs(cub_tmp, bytes, keys, keys_alt, vals, vals_alt, nm, 0,
+                                                              32 + seg_bits, st);
+        if (e != cudaSuccess) return e;
+        kd_gather_kernel<<<(nm + 255) / 256, 256, 0, st>>>(src, vals_alt, nm, dst);
+        float4* t = src; src = dst; dst = t;
+    }
+    if (src != pts) return cudaMemcpyAsync(pts, src, (size_t)nm * sizeof(float4), cudaMemcpyDeviceToDevice, st);
+    return cudaSuccess;
+}
+
 // Builds the hierarchy for the model currently in `m` (mhat / geo valid); keys/vals/perm/cub: sort scratch for nm items.
 int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_t* keys_alt,
-               int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, cudaStream_t st)
+               int32_t* vals, int32_t* perm, void* cub_tmp, size_t cub_bytes, void* kd_scratch, cudaStream_t st)
 {
     const int nm = (int)m.nm;
     tree_keys_kernel<<<(nm + 255) / 256, 256, 0, st>>>(m.mhat, nm, m.geo, keys, vals);
@@ -494,6 +620,7 @@ int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_
     if (!wide) {
     const int n_slots = t.n_leaves * TREE_LEAF;
     tree_points_kernel<<<(n_slots + 255) / 256, 256, 0, st>>>(m.mhat, perm, nm, n_slots, t.pts);
+    if (kd_scratch && (e = kd_global_levels(t.pts, nm, kd_scratch, st)) != cudaSuccess) return (int)e;
     if (nm >= KD_MIN_POINTS) wtree_local_kd_kernel<<<(nm + KD_B - 1) / KD_B, KD_T, 0, st>>>(t.pts, nm);
     tree_leaf_boxes_kernel<<<(t.n_leaves + 255) / 256, 256, 0, st>>>(t.pts, t.n_leaves, (nm + TREE_LEAF - 1) / TREE_LEAF,
                                                                      t.nodes);
@@ -504,6 +631,7 @@ int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_
     // wide form (same sorted order)
     const int n0 = t.w.count[0];
     tree_points_kernel<<<(n0 * 32 + 255) / 256, 256, 0, st>>>(m.mhat, perm, nm, n0 * 32, t.wpts);
+    if (kd_scratch && (e = kd_global_levels(t.wpts, nm, kd_scratch, st)) != cudaSuccess) return (int)e;
     if (nm >= KD_MIN_POINTS) wtree_local_kd_kernel<<<(nm + KD_B - 1) / KD_B, KD_T, 0, st>>>(t.wpts, nm);
     {
         const int padded = (n0 + 31) / 32 * 32;
@@ -543,6 +671,8 @@ void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int
                                                     s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm, s.idx,
                                                     use_prev, ctl, honor_done, progress);
 }
+
+int kd_global_min_points() { return KD_GLOBAL_MIN_POINTS; }
 
 size_t tree_sort_bytes(int n)
 {

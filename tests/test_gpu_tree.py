@@ -166,6 +166,22 @@ def test_tree_equals_brute_force_on_noisy_large_clouds(icp):
     ctx.close()
 
 
+def test_tree_large_model_small_scene(icp):
+    # a model large enough for the global k-d levels of the build, searched by the warp-per-point form (small scene)
+    # and, with the same model, by the thread-per-point form (forced): both equal brute force
+    m, p, _ = synthetic_pair(1 << 18, seed=9)
+    p = np.ascontiguousarray(p[::37])
+    ctx = icp.Context(0)
+    ctx.set_model(m)
+    ctx.set_scene(p)
+    idx_b, _ = ctx.closest(want_Y=False)
+    ctx.set_nn_mode("tree")
+    ctx.reset_scene()
+    idx_t, _ = ctx.closest(want_Y=False)
+    assert ctx.nn_mode() == "tree" and np.array_equal(idx_t, idx_b)
+    ctx.close()
+
+
 def test_tree_in_hidden_contexts_follows_environment(icp, clouds, monkeypatch):
     # one-shot wrappers and icp_batch_run lanes keep their contexts between calls: ICP_NN is read at every use
     m, p = clouds("cow_ref"), clouds("cow_tr1")
