@@ -318,14 +318,17 @@ __global__ void __launch_bounds__(KD_T) wtree_local_kd_kernel(float4* __restrict
         __syncthreads();
         for (int k = 2; k <= S; k <<= 1)
             for (int j = k >> 1; j > 0; j >>= 1) {
+                // a warp's 32 pairs span 64 consecutive elements: stages with j < 32 exchange inside the warp's own span
+                // and need no block-wide barrier (201 of the 251 stages)
+                if (j >= 32) __syncthreads(); else __syncwarp();
                 const int i = ((tid & ~(j - 1)) << 1) | (tid & (j - 1));           // bit j clear; partner has it set
                 const int ip = i | j;
                 const bool asc = (k == S) || ((i & k) == 0);                       // last merge: every segment ascending
                 const int ax = axis[i / S];
                 const float4 a = P[i], b = P[ip];
                 if ((kd_comp(a, ax) > kd_comp(b, ax)) == asc) { P[i] = b; P[ip] = a; }
-                __syncthreads();
             }
+        __syncthreads();
     }
     for (int e = tid; e < valid; e += KD_T) pts[base + e] = P[e];
 }
