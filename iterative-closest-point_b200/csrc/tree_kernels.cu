@@ -16,6 +16,8 @@
 //     merged by (v, lowest index) — order independent, hence the traversal order is free;
 //   * a node is skipped only when a LOWER bound of its box distance (all operations rounded DOWN) exceeds
 //     thr2, which (1+16u) keeps above d~2 of every point inside the box.
+// The ORDER of the model points (Morton sort, then median splits: wtree_local_kd_kernel / kd_global_levels) only decides
+// how many boxes a search opens; exactness never depends on it.
 // Model scales outside [1e-12, 1e12] are refused at build time (FP32 squares would leave the normal range);
 // icp_api.cu then keeps the brute-force path, whose bound has no such restriction.
 #include <cub/device/device_radix_sort.cuh>
