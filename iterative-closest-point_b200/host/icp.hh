@@ -39,6 +39,35 @@ public:
     double& operator()(long i) { return d_[(size_t)i]; }
     double operator()(long i) const { return d_[(size_t)i]; }
 
+#ifdef ICP_B200_EIGEN_STANDIN
+    // host/compat only: the two Eigen expressions the reference's benchmark harness evaluates itself
+    // (`M.rowwise().mean()`, `M.colwise() - v`, src/bench.cc:150-154,164-165).  They are the CALLER's Eigen code, not
+    // entry points of the path; with the real Eigen present this block is not compiled (see compat/cpu.hh).
+    struct RowwiseProxy {
+        const Matrix& m;
+        Matrix mean() const
+        {
+            Matrix out(m.rows(), 1);
+            for (long j = 0; j < m.cols(); ++j)
+                for (long i = 0; i < m.rows(); ++i) out(i) += m(i, j);
+            for (long i = 0; i < m.rows(); ++i) out(i) /= (double)m.cols();
+            return out;
+        }
+    };
+    struct ColwiseProxy {
+        const Matrix& m;
+        Matrix operator-(const Matrix& v) const
+        {
+            Matrix out(m.rows(), m.cols());
+            for (long j = 0; j < m.cols(); ++j)
+                for (long i = 0; i < m.rows(); ++i) out(i, j) = m(i, j) - v(i);
+            return out;
+        }
+    };
+    RowwiseProxy rowwise() const { return {*this}; }
+    ColwiseProxy colwise() const { return {*this}; }
+#endif
+
 private:
     long r_ = 0, c_ = 0;
     std::vector<double> d_;
@@ -86,6 +115,20 @@ struct err_compute_alignment_params {
     const Matrix& y;
 };
 
+// src/GPU/gpu.hh:25-39
+struct gpu_closest_matrix_params {
+    const Matrix& p;
+    const Matrix& m;
+    Matrix& y;
+};
+struct gpu_err_compute_params {
+    const Matrix& Y;
+    Matrix& p;
+    bool s;               // the in_place flag of compute_err_w (the reference names it `s`)
+    const Matrix sr;      // s * R
+    const Matrix& t;
+};
+
 // src/cpu.cc:5-27
 inline Matrix closest_matrix(closest_matrix_params pa)
 {
@@ -126,13 +169,29 @@ public:
         if ((rc = icp_set_model(ctx, m.data(), nm))) die("icp_set_model", rc);
         if ((rc = icp_set_scene(ctx, new_p.data(), np))) die("icp_set_scene", rc);
     }
-    ICP(const ICP&) = delete;
+    // The reference's ICP objects are plain host values and its harness copies them freely (src/bench.cc:186-189,
+    // 211-226, 362-381).  A copy takes the host state (m, p, new_p, s, r, t); its device context is created on
+    // first use from the copy's current new_p.
+    ICP(const ICP& o)
+        : new_p(o.new_p), iterations(o.iterations), errors(o.errors), s(o.s), t(o.t), r(o.r), m(o.m), p(o.p), np(o.np),
+          nm(o.nm), dim(o.dim), max_iter(o.max_iter)
+    {
+    }
     ICP& operator=(const ICP&) = delete;
     ~ICP() { icp_destroy(ctx); }
 
     closest_matrix_params get_closest_matrix_params() { return {dim, np, nm, new_p, m}; }
     err_compute_params get_err_compute_params(Matrix& Y) { return {np, new_p, s, r, t, Y}; }
     err_compute_alignment_params get_err_compute_alignment_params(Matrix& Y) { return {np, new_p, s, r, t, Y}; }
+    // GPU::ICP's forms, src/GPU/gpu.hh:57-72
+    gpu_closest_matrix_params get_closest_matrix_params(Matrix& Y) { return {new_p, m, Y}; }
+    gpu_err_compute_params get_err_compute_params(Matrix& Y, bool in_place)
+    {
+        Matrix sr(3, 3);
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) sr(i, j) = s * r(i, j);
+        return {Y, new_p, in_place, sr, t};
+    }
     double getDim() { return dim; }
     double getNp() { return np; }
 
@@ -154,6 +213,7 @@ public:
     void find_corresponding(bool check_sizes = true)
     {
         if (check_sizes) alignement_check();
+        ensure_ctx();
         std::vector<double> hist((size_t)(max_iter > 0 ? max_iter : 1));
         int rc = icp_run(ctx, max_iter, threshold, 0, &iterations, hist.data());
         if (rc) die("icp_run", rc);
@@ -171,6 +231,7 @@ public:
     Matrix compute_y_naive()                                     // src/GPU/gpu.cc:6-14
     {
         Matrix Y(dim, np);
+        ensure_ctx();
         int rc = icp_closest(ctx, nullptr, Y.data());
         if (rc) die("icp_closest", rc);
         return Y;
@@ -190,7 +251,7 @@ public:
     double scale() const { return s; }
     const Matrix& rotation() const { return r; }
     const Matrix& translation() const { return t; }
-    icp_ctx* handle() { return ctx; }
+    icp_ctx* handle() { ensure_ctx(); return ctx; }
 
 public:
     Matrix new_p;
@@ -198,6 +259,14 @@ public:
     std::vector<double> errors;
 
 private:
+    void ensure_ctx()     // copies only: a constructed object already owns its context
+    {
+        if (ctx) return;
+        int rc = icp_create(&ctx, 0);
+        if (rc) die("icp_create", rc);
+        if ((rc = icp_set_model(ctx, m.data(), nm))) die("icp_set_model", rc);
+        if ((rc = icp_set_scene(ctx, new_p.data(), np))) die("icp_set_scene", rc);
+    }
     void pull_transform()
     {
         double R_[9], t_[3];
@@ -227,6 +296,8 @@ using icpb::err_compute_params;
 using icpb::ICP;
 }  // namespace CPU
 namespace GPU {
+using icpb::gpu_closest_matrix_params;
+using icpb::gpu_err_compute_params;
 using icpb::ICP;
 using icpb::Matrix;
 }  // namespace GPU
