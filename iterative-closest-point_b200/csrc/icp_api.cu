@@ -219,7 +219,7 @@ void choose_splits(icp_ctx* c)
     const long long n_tiles = c->s.np_pad / NN_TILE;
     const long long cpt = c->m.nm_pad / NN_G;
     const long long total = n_tiles * cpt;
-    const long long wave = (long long)c->sm_count * 4;
+    const long long wave = (long long)c->sm_count * NN_MIN_CTAS;
     const long long per_cta = 65536 / NN_G;             // ~64 K model points x 1 scene tile per CTA and wave
     long long waves = (total + per_cta * wave - 1) / (per_cta * wave);
     if (waves < 1) waves = 1;

@@ -16,11 +16,29 @@
 namespace icpb {
 
 // ---- nearest-neighbour filter geometry ---------------------------------------------------------
+// The ICP_NN_* macros exist for A/B builds only (`make variants`, tools/filter_ab.sh: one library per variant,
+// selected at run time with ICP_B200_LIB); the product is the defaults, which every committed number refers to.
+#ifndef ICP_NN_R
+#define ICP_NN_R 8
+#endif
+#ifndef ICP_NN_G
+#define ICP_NN_G 64
+#endif
+#ifndef ICP_NN_Q_UNROLL
+#define ICP_NN_Q_UNROLL 2
+#endif
+#ifndef ICP_NN_MIN_CTAS
+#define ICP_NN_MIN_CTAS 4
+#endif
 constexpr int NN_THREADS = 128;                 // threads per CTA
-constexpr int NN_R       = 8;                   // scene points register-blocked per thread
+constexpr int NN_R       = ICP_NN_R;            // scene points register-blocked per thread (8)
 constexpr int NN_TILE    = NN_THREADS * NN_R;   // scene points per CTA (1024)
-constexpr int NN_G       = 64;                  // model points per tracking chunk
+constexpr int NN_G       = ICP_NN_G;            // model points per tracking chunk (64)
 constexpr int NN_TM      = 512;                 // model points per shared-memory stage
+constexpr int NN_Q_UNROLL = ICP_NN_Q_UNROLL;    // LDS.128 quadruples per trip of the filter's inner loop (2)
+constexpr int NN_MIN_CTAS = ICP_NN_MIN_CTAS;    // resident filter CTAs per SM the launch bounds ask for (4)
+static_assert(NN_TM % NN_G == 0 && NN_G % 32 == 0 && NN_G <= 256, "chunk size");
+static_assert((NN_G / 4) % NN_Q_UNROLL == 0, "inner-loop unroll must divide the chunk");
 constexpr float NN_SENTINEL = 1.0e18f;          // coordinate of padded model points (never wins)
 
 // ---- reductions --------------------------------------------------------------------------------

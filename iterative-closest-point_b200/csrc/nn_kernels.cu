@@ -90,7 +90,7 @@ __device__ __forceinline__ int cta_of_unit(long long x, long long T, int n)     
     return (int)(((x + 1) * n - 1) / T);
 }
 
-__global__ void __launch_bounds__(NN_THREADS, 4)
+__global__ void __launch_bounds__(NN_THREADS, NN_MIN_CTAS)
 nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx, const float* __restrict__ phy,
                  const float* __restrict__ phz, int np_pad, int n_tiles, int cpt,
                  float* __restrict__ out_best, float* __restrict__ out_runner, uint32_t* __restrict__ out_chunk,
@@ -190,7 +190,7 @@ nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx,
                 float tmin[NN_R];
 #pragma unroll
                 for (int r = 0; r < NN_R; ++r) tmin[r] = __int_as_float(0x7f800000);
-#pragma unroll 2
+#pragma unroll NN_Q_UNROLL
                 for (int q = 0; q < NN_G / 4; ++q) {
                     const int o = c * (NN_G / 4) + q;
                     const float4 X = X4[o], Y = Y4[o], Z = Z4[o], W = W4[o];
