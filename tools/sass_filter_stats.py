@@ -66,7 +66,6 @@ def stats(lib):
     outer = next(((a, b) for a, b in ls[1:] if a <= q0 and b >= q1 and (a, b) != (q0, q1)), None)
     lds, f2, m3 = cnt(qbody, "LDS.128"), cnt(qbody, "FFMA2"), cnt(qbody, "FMNMX3")
     spills = cnt(qbody, "LDL") + cnt(qbody, "STL")
-    pairs_per_trip = f2 // 3 * 2 // 1       # one FFMA2 = 2 of the 3 FMAs... pairs = FFMA2 * 2 / 3
     r_points = f2 // (3 * lds // 2) if lds else 0      # scene points per thread: FFMA2 per LDS quadruple / 6
     d = dict(lib=lib.split("/")[-1], reg=reg, stack=stack, q_len=len(qbody), lds=lds, ffma2=f2, fmnmx3=m3,
              q_other=len(qbody) - lds - f2 - m3, q_spills=spills, r=r_points)
@@ -85,19 +84,18 @@ def main():
     if not libs:
         print(__doc__)
         return 1
-    print(f"{'library':28s} {'reg':>4s} {'stk':>4s} {'R':>3s} {'q-loop':>7s} {'LDS':>4s} {'FFMA2':>6s} {'FMNMX3':>7s} "
-          f"{'other':>6s} {'spill':>6s} {'c-ovh':>6s} {'form. share @G=64':>18s} {'@G=128':>8s}")
+    print(f"{'library':28s} {'G':>4s} {'reg':>4s} {'stk':>4s} {'R':>3s} {'q-loop':>7s} {'LDS':>4s} {'FFMA2':>6s} {'FMNMX3':>7s} "
+          f"{'other':>6s} {'spill':>6s} {'c-ovh':>6s} {'formulation share':>18s}")
     for lib in libs:
         d = stats(lib)
         form_trip = d["ffma2"] + d["fmnmx3"]
-        share = {}
-        for G in (64, 128):
-            trips = (G // 4) / max(d.get("quads_per_trip", 1), 1)
-            total = trips * d["q_len"] + d.get("c_overhead", 0)
-            share[G] = trips * form_trip / total if total else float("nan")
-        print(f"{d['lib']:28s} {d['reg']:4d} {d['stack']:4d} {d['r']:3d} {d['q_len']:7d} {d['lds']:4d} {d['ffma2']:6d} "
-              f"{d['fmnmx3']:7d} {d['q_other']:6d} {d['q_spills']:6d} {d.get('c_overhead', -1):6d} "
-              f"{share[64]:18.3f} {share[128]:8.3f}")
+        g = re.search(r"g(\d+)", d["lib"].replace("libicp_b200", ""))      # chunk size: from the variant's name (default 64)
+        G = int(g.group(1)) if g else 64
+        trips = (G // 4) / max(d.get("quads_per_trip", 1), 1)
+        total = trips * d["q_len"] + d.get("c_overhead", 0)
+        share = trips * form_trip / total if total else float("nan")
+        print(f"{d['lib']:28s} {G:4d} {d['reg']:4d} {d['stack']:4d} {d['r']:3d} {d['q_len']:7d} {d['lds']:4d} {d['ffma2']:6d} "
+              f"{d['fmnmx3']:7d} {d['q_other']:6d} {d['q_spills']:6d} {d.get('c_overhead', -1):6d} {share:18.3f}")
     return 0
 
 
