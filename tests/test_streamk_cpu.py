@@ -17,6 +17,7 @@ import pytest
 NN_TILE, NN_G, NN_TM = 1024, 64, 512
 CPM = NN_TM // NN_G
 SMS = 148
+MIN_CTAS = 4          # resident filter CTAs per SM (NN_MIN_CTAS)
 
 
 def pad(n, q):
@@ -28,7 +29,7 @@ def choose_splits(np_, nm, forced=0, sm_count=SMS):
     n_tiles = pad(np_, NN_TILE) // NN_TILE
     cpt = pad(nm, NN_TM) // NN_G
     total = n_tiles * cpt
-    wave = sm_count * 4
+    wave = sm_count * MIN_CTAS
     per_cta = 65536 // NN_G
     waves = max(1, (total + per_cta * wave - 1) // (per_cta * wave))
     n_cta = wave * waves
@@ -116,3 +117,20 @@ def test_largest_configuration_fits_the_kernel_state():
         segs = list(segments(int(b), n_cta, n_tiles, cpt))
         assert sum(c_hi - c_lo for _, c_lo, c_hi, _ in segs) == (b + 1) * T // n_cta - b * T // n_cta
         assert all(0 <= s < n_splits for *_, s in segs)
+
+
+@pytest.mark.parametrize("r,g,ctas", [(8, 128, 4), (12, 64, 3), (12, 128, 3), (16, 64, 2)])
+def test_variant_geometries(monkeypatch, r, g, ctas):
+    """The build-time variants of the filter (icp_common.cuh ICP_NN_R / _G / _MIN_CTAS, `make variants`) run the same
+    integer arithmetic with other constants: 128-point chunks, 1 536- and 2 048-point scene tiles, 3 or 2 CTAs per SM."""
+    import sys
+    mod = sys.modules[__name__]
+    monkeypatch.setattr(mod, "NN_TILE", 128 * r)
+    monkeypatch.setattr(mod, "NN_G", g)
+    monkeypatch.setattr(mod, "CPM", NN_TM // g)
+    monkeypatch.setattr(mod, "MIN_CTAS", ctas)
+    for np_, nm in [(1, 1), (1535, 513), (2903, 2903), (9000, 20000), (48485, 48485), (40097, 40256), (65536, 65536)]:
+        n_cta, _ = check(np_, nm)
+        assert n_cta <= SMS * ctas or n_cta % (SMS * ctas) == 0
+    for forced in (1, 3, 37, 444, 5000):
+        check(5000, 4097, forced)
