@@ -126,6 +126,13 @@ struct icp_ctx {
     int* progress_arg = nullptr;           // what nn_pass hands to the filter kernel (set by icp_run only)
     int lookahead = 3;                     // ICP_LOOKAHEAD: iterations icp_run keeps enqueued ahead of the device (0 = all at once)
     bool profile = false;                  // ICP_PROFILE=1: events between all kernels of icp_run (adds ~us per iteration)
+    // ICP_GRAPH=1 (experiment, off by default): iterations >= 1 of icp_run are ONE instantiated CUDA graph (the
+    // iteration's kernels as captured from the plain enqueue path), re-launched per iteration under the same
+    // look-ahead rule.  The graph is kept while every captured kernel argument stays the same (GraphKey).
+    int graph_mode = 0;
+    cudaGraphExec_t loop_graph = nullptr;
+    int graph_kernels = 0;                 // kernels inside loop_graph
+    struct GraphKey { const void* p[24]; long long n[12]; double d[2]; } graph_key{};
 };
 
 namespace {
@@ -352,6 +359,56 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
     return launched;
 }
 
+// ICP_GRAPH: everything a captured iteration depends on.  Buffers of one group are (re)allocated together, so
+// the pointers below change whenever any kernel argument does; sizes, grid shapes and modes are listed explicitly.
+void fill_graph_key(const icp_ctx* c, double n_global, double threshold, icp_ctx::GraphKey& k)
+{
+    memset(&k, 0, sizeof(k));
+    const void* p[] = {c->m.m64x, c->m.m64y, c->m.m64z, c->m.mhat, c->m.geo, c->s.p64x, c->s.p64y, c->s.p64z, c->s.phx,
+                       c->s.phy, c->s.phz, c->s.idx, c->sc.best, c->sc.runner, c->sc.chunk, c->sc.amb_list, c->sc.amb_thr,
+                       c->sc.seg_v, c->sc.seg_k, c->sc.batch_ticket, c->d_err_hist, c->d_partials, c->progress_arg,
+                       c->peer_ready ? (const void*)c->peer.box[0] : nullptr};
+    static_assert(sizeof(p) == sizeof(k.p), "GraphKey::p");
+    memcpy(k.p, p, sizeof(p));
+    const long long n[] = {c->m.nm, c->m.nm_pad, c->s.np, c->s.np_pad, c->sc.n_cta, c->sc.n_splits, (long long)c->sc.seg_cap,
+                           c->n_red_blocks, c->align_mode, (c->comm ? 1 : 0) | (c->peer_ready ? 2 : 0) | (c->is_lane ? 4 : 0),
+                           c->peer.world * 64 + c->peer.rank, fused_blocks(c)};
+    static_assert(sizeof(n) == sizeof(k.n), "GraphKey::n");
+    memcpy(k.n, n, sizeof(n));
+    k.d[0] = n_global;
+    k.d[1] = threshold;
+}
+
+// Captures one iteration (K1 filter/refine/exact + the alignment step, exactly as the plain path enqueues them) into
+// c->loop_graph.  Any failure leaves the stream usable, clears the error and switches graph mode off for this context.
+bool capture_iteration(icp_ctx* c, double n_global, double threshold)
+{
+    if (c->loop_graph) { cudaGraphExecDestroy(c->loop_graph); c->loop_graph = nullptr; }
+    const int launched_before = c->stats.kernels_launched;
+    cudaGraph_t g = nullptr;
+    bool ok = cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+    if (ok) {
+        nn_pass(c, 1, 1, nullptr, nullptr);
+        const int launched = align_step(c, 1, 1, 1, n_global, threshold);
+        ok = launched > 0;
+        if (ok) c->stats.kernels_launched += launched;
+        const cudaError_t e = cudaStreamEndCapture(c->st, &g);      // always: the stream must leave capture mode
+        ok = ok && e == cudaSuccess && g != nullptr;
+    }
+    if (ok) ok = cudaGraphInstantiate(&c->loop_graph, g, 0) == cudaSuccess;
+    if (g) cudaGraphDestroy(g);
+    c->graph_kernels = c->stats.kernels_launched - launched_before;
+    c->stats.kernels_launched = launched_before;
+    if (!ok) {
+        cudaGetLastError();
+        if (c->loop_graph) { cudaGraphExecDestroy(c->loop_graph); c->loop_graph = nullptr; }
+        c->graph_mode = 0;
+        return false;
+    }
+    fill_graph_key(c, n_global, threshold, c->graph_key);
+    return true;
+}
+
 int reset_ctl(icp_ctx* c)
 {
     CK(cudaMemsetAsync(c->d_ctl, 0, CTL_N * sizeof(int), c->st));
@@ -418,6 +475,7 @@ int icp_create(icp_ctx** out, int device)
     if (const char* e = getenv("ICP_ALIGN")) c->align_mode = !strcmp(e, "fused") ? 1 : (!strcmp(e, "split") ? 2 : 0);
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
+    if (const char* e = getenv("ICP_GRAPH")) c->graph_mode = atoi(e);
     if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
     if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
@@ -450,6 +508,7 @@ void icp_destroy(icp_ctx* c)
     if (c->tree.kd_scratch) cudaFree(c->tree.kd_scratch);
     if (c->d_cub) cudaFree(c->d_cub);
     for (auto e : c->ev_filter) cudaEventDestroy(e);
+    if (c->loop_graph) cudaGraphExecDestroy(c->loop_graph);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->st) cudaStreamDestroy(c->st);
@@ -743,6 +802,9 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     const int LA = (c->lookahead > 0 && !nccl_path(c)) ? (c->lookahead < 2 ? 2 : c->lookahead) : 0;   // >= 2: see nn_filter_kernel
     *(volatile int*)c->h_progress = 0;
     c->progress_arg = LA ? c->d_progress : nullptr;
+    // ICP_GRAPH (experiment): brute-force search only, no per-kernel profiling events, not on the NCCL path
+    bool use_graph = c->graph_mode > 0 && !c->profile && !nccl_path(c) && !tree_active(c);
+    int timed_iters = max_iter;                // iterations whose filter events were recorded
     for (int it = 0; it < max_iter; ++it) {
         if (LA && it >= LA) {
             const int w = wait_progress(c, it + 1 - LA, it);
@@ -750,6 +812,20 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
             if (w) break;
         }
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
+        if (use_graph && it >= 1) {
+            // iteration 0 always takes the plain path (first-call attribute set-up, and its two events time the filter)
+            if (it == 1) {
+                icp_ctx::GraphKey key;
+                fill_graph_key(c, np_glob, threshold, key);
+                if ((!c->loop_graph || memcmp(&key, &c->graph_key, sizeof(key)) != 0) && !capture_iteration(c, np_glob, threshold))
+                    use_graph = false;
+            }
+            if (use_graph) {
+                CK(cudaGraphLaunch(c->loop_graph, c->st));
+                c->stats.kernels_launched += c->graph_kernels;
+                continue;
+            }
+        }
         nn_pass(c, 1, (it > 0 || c->have_idx) ? 1 : 0, ev[0], ev[1], c->profile ? ev[2] : nullptr, c->profile ? ev[3] : nullptr);
         if (!nccl_path(c)) {
             int launched = align_step(c, 1, 1, 1, np_glob, threshold);
@@ -785,7 +861,8 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
     cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
     float f = 0.f, f_ref = 0.f, f_ex = 0.f, f_al = 0.f;
-    for (int it = 0; it < iters; ++it) {
+    if (use_graph) timed_iters = 1;            // graphed iterations carry no events: ms_filter is extrapolated from iteration 0
+    for (int it = 0; it < iters && it < timed_iters; ++it) {
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
         float ms = 0.f;
         cudaEventElapsedTime(&ms, ev[0], ev[1]);
@@ -796,7 +873,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
             cudaEventElapsedTime(&ms, ev[3], ev[4]); f_al += ms;
         }
     }
-    c->stats.ms_filter = f;
+    c->stats.ms_filter = (use_graph && iters > 1) ? f * (float)iters : f;
     c->stats.ms_refine = f_ref;
     c->stats.ms_exact = f_ex;
     c->stats.ms_align = f_al;
