@@ -287,7 +287,11 @@ __device__ __forceinline__ float surrogate32(const float4 mh, float cx, float cy
 }
 
 constexpr int REFINE_THREADS = 256;
-constexpr int RF = 8;    // lanes cooperating on one scene point
+#ifndef ICP_RF
+#define ICP_RF 8
+#endif
+constexpr int RF = ICP_RF;    // lanes cooperating on one scene point (8; build-time variant like ICP_NN_*)
+static_assert(RF == 4 || RF == 8 || RF == 16, "RF");
 
 // nn_refine: merges the model splits, derives the bound tau and the FP32 acceptance threshold
 // thr = best + tau (rounded up).  Every model point that can be the reference's argmin has d' <= thr.
