@@ -179,8 +179,11 @@ class Context:
     def nn_mode(self):
         return ("brute", "tree")[self._L.icp_get_nn_mode(self._h)]
 
-    def get_scene(self):
-        out = np.empty((self.np, 3))
+    def get_scene(self, out=None):
+        """new_p (src/cpu.hh:97) as (np, 3) float64; `out`: a C-contiguous float64 buffer of that shape to fill (e.g. pinned)."""
+        if out is None:
+            out = np.empty((self.np, 3))
+        assert out.dtype == np.float64 and out.shape == (self.np, 3) and out.flags.c_contiguous
         _ck(self._L.icp_get_scene(self._h, _d(out)))
         return out
 
