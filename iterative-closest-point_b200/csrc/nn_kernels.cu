@@ -292,6 +292,7 @@ constexpr int REFINE_THREADS = 256;
 #endif
 constexpr int RF = ICP_RF;    // lanes cooperating on one scene point (8; build-time variant like ICP_NN_*)
 static_assert(RF == 4 || RF == 8 || RF == 16, "RF");
+static_assert(NN_G / RF <= 32, "nn_refine keeps one candidate bit per (lane, step) of the best chunk in a 32-bit mask");
 
 // nn_refine: merges the model splits, derives the bound tau and the FP32 acceptance threshold
 // thr = best + tau (rounded up).  Every model point that can be the reference's argmin has d' <= thr.
