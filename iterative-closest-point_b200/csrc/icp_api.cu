@@ -130,7 +130,10 @@ struct icp_ctx {
     // iteration's kernels as captured from the plain enqueue path), re-launched per iteration under the same
     // look-ahead rule.  The graph is kept while every captured kernel argument stays the same (GraphKey).
     int graph_mode = 0;
+    cudaGraph_t loop_graph_tmpl = nullptr; // kept: its event-record node handles address the nodes of loop_graph
     cudaGraphExec_t loop_graph = nullptr;
+    cudaGraphNode_t graph_ev_node[2] = {nullptr, nullptr};   // event records before / after the filter kernel
+    bool capturing = false;                // nn_pass records its events as external event nodes
     int graph_kernels = 0;                 // kernels inside loop_graph
     struct GraphKey { const void* p[24]; long long n[12]; double d[2]; } graph_key{};
 };
@@ -268,7 +271,13 @@ int allreduce(icp_ctx* c, double* buf, size_t n)
 void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent_t e1, cudaEvent_t e2 = nullptr,
              cudaEvent_t e3 = nullptr)
 {
-    if (e0) cudaEventRecord(e0, c->st);
+    // inside a stream capture (ICP_GRAPH) a plain cudaEventRecord is only a dependency marker; the external form
+    // becomes an event-record node that really records on every launch of the graph
+    auto record = [c](cudaEvent_t e) {
+        if (c->capturing) cudaEventRecordWithFlags(e, c->st, cudaEventRecordExternal);
+        else cudaEventRecord(e, c->st);
+    };
+    if (e0) record(e0);
     if (tree_active(c) && c->tree_built[tree_use_wide(c)]) {
         // measured (profiles/r01h_tree.md): a warp per point wins while the grid is a few waves (cow 0.014 vs 0.052 ms,
         // horse 128 vs 285 us per search: the slowest thread no longer sets the kernel time); a thread per point
@@ -284,7 +293,7 @@ void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent
         return;
     }
     launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st, c->progress_arg);
-    if (e1) cudaEventRecord(e1, c->st);
+    if (e1) record(e1);
     launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
     if (e2) cudaEventRecord(e2, c->st);
     launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st, c->profile ? c->d_trace : nullptr);
@@ -383,25 +392,50 @@ void fill_graph_key(const icp_ctx* c, double n_global, double threshold, icp_ctx
 // c->loop_graph.  Any failure leaves the stream usable, clears the error and switches graph mode off for this context.
 bool capture_iteration(icp_ctx* c, double n_global, double threshold)
 {
-    if (c->loop_graph) { cudaGraphExecDestroy(c->loop_graph); c->loop_graph = nullptr; }
+    auto drop = [c]() {
+        if (c->loop_graph) { cudaGraphExecDestroy(c->loop_graph); c->loop_graph = nullptr; }
+        if (c->loop_graph_tmpl) { cudaGraphDestroy(c->loop_graph_tmpl); c->loop_graph_tmpl = nullptr; }
+        c->graph_ev_node[0] = c->graph_ev_node[1] = nullptr;
+    };
+    drop();
     const int launched_before = c->stats.kernels_launched;
     cudaGraph_t g = nullptr;
+    // placeholders for the two filter events: iteration 1's own pair (icp_run re-targets the nodes before every launch)
+    cudaEvent_t ea = c->ev_filter[2], eb = c->ev_filter[3];
     bool ok = cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
     if (ok) {
-        nn_pass(c, 1, 1, nullptr, nullptr);
+        c->capturing = true;
+        nn_pass(c, 1, 1, ea, eb);
+        c->capturing = false;
         const int launched = align_step(c, 1, 1, 1, n_global, threshold);
         ok = launched > 0;
         if (ok) c->stats.kernels_launched += launched;
         const cudaError_t e = cudaStreamEndCapture(c->st, &g);      // always: the stream must leave capture mode
         ok = ok && e == cudaSuccess && g != nullptr;
     }
-    if (ok) ok = cudaGraphInstantiate(&c->loop_graph, g, 0) == cudaSuccess;
-    if (g) cudaGraphDestroy(g);
     c->graph_kernels = c->stats.kernels_launched - launched_before;
     c->stats.kernels_launched = launched_before;
+    if (ok) {                                                       // find the two event-record nodes
+        size_t n = 0;
+        ok = cudaGraphGetNodes(g, nullptr, &n) == cudaSuccess && n > 0 && n < 64;
+        cudaGraphNode_t nodes[64];
+        if (ok) ok = cudaGraphGetNodes(g, nodes, &n) == cudaSuccess;
+        for (size_t i = 0; ok && i < n; ++i) {
+            cudaGraphNodeType t;
+            cudaEvent_t ev = nullptr;
+            if (cudaGraphNodeGetType(nodes[i], &t) != cudaSuccess) { ok = false; break; }
+            if (t != cudaGraphNodeTypeEventRecord) continue;
+            if (cudaGraphEventRecordNodeGetEvent(nodes[i], &ev) != cudaSuccess) { ok = false; break; }
+            if (ev == ea) c->graph_ev_node[0] = nodes[i];
+            if (ev == eb) c->graph_ev_node[1] = nodes[i];
+        }
+        ok = ok && c->graph_ev_node[0] && c->graph_ev_node[1];
+    }
+    if (ok) ok = cudaGraphInstantiate(&c->loop_graph, g, 0) == cudaSuccess;
+    c->loop_graph_tmpl = g;
     if (!ok) {
         cudaGetLastError();
-        if (c->loop_graph) { cudaGraphExecDestroy(c->loop_graph); c->loop_graph = nullptr; }
+        drop();
         c->graph_mode = 0;
         return false;
     }
@@ -509,6 +543,7 @@ void icp_destroy(icp_ctx* c)
     if (c->d_cub) cudaFree(c->d_cub);
     for (auto e : c->ev_filter) cudaEventDestroy(e);
     if (c->loop_graph) cudaGraphExecDestroy(c->loop_graph);
+    if (c->loop_graph_tmpl) cudaGraphDestroy(c->loop_graph_tmpl);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->st) cudaStreamDestroy(c->st);
@@ -804,7 +839,6 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->progress_arg = LA ? c->d_progress : nullptr;
     // ICP_GRAPH (experiment): brute-force search only, no per-kernel profiling events, not on the NCCL path
     bool use_graph = c->graph_mode > 0 && !c->profile && !nccl_path(c) && !tree_active(c);
-    int timed_iters = max_iter;                // iterations whose filter events were recorded
     for (int it = 0; it < max_iter; ++it) {
         if (LA && it >= LA) {
             const int w = wait_progress(c, it + 1 - LA, it);
@@ -821,6 +855,8 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
                     use_graph = false;
             }
             if (use_graph) {
+                CK(cudaGraphExecEventRecordNodeSetEvent(c->loop_graph, c->graph_ev_node[0], ev[0]));
+                CK(cudaGraphExecEventRecordNodeSetEvent(c->loop_graph, c->graph_ev_node[1], ev[1]));
                 CK(cudaGraphLaunch(c->loop_graph, c->st));
                 c->stats.kernels_launched += c->graph_kernels;
                 continue;
@@ -861,8 +897,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
     cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
     float f = 0.f, f_ref = 0.f, f_ex = 0.f, f_al = 0.f;
-    if (use_graph) timed_iters = 1;            // graphed iterations carry no events: ms_filter is extrapolated from iteration 0
-    for (int it = 0; it < iters && it < timed_iters; ++it) {
+    for (int it = 0; it < iters; ++it) {
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
         float ms = 0.f;
         cudaEventElapsedTime(&ms, ev[0], ev[1]);
@@ -873,7 +908,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
             cudaEventElapsedTime(&ms, ev[3], ev[4]); f_al += ms;
         }
     }
-    c->stats.ms_filter = (use_graph && iters > 1) ? f * (float)iters : f;
+    c->stats.ms_filter = f;
     c->stats.ms_refine = f_ref;
     c->stats.ms_exact = f_ex;
     c->stats.ms_align = f_al;
