@@ -410,9 +410,15 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
 // Work item = (batch of EX_P queued points) x (model segment); a model point is loaded once per batch.
 // Segment results are merged by the last CTA to finish a batch (ticket per batch).
 constexpr int EXACT_THREADS = 256;
-constexpr int EX_P = 4;          // queued points per batch
+#ifndef ICP_EX_P
+#define ICP_EX_P 4
+#endif
+#ifndef ICP_EX_MIN_SEG
+#define ICP_EX_MIN_SEG 4096
+#endif
+constexpr int EX_P = ICP_EX_P;   // queued points per batch (4; build-time variant like ICP_NN_*)
 constexpr int EX_U = 4;          // model points in flight per thread
-constexpr int EX_MIN_SEG = 4096; // model points per segment at least (1024 was measured slower: more tickets and merges)
+constexpr int EX_MIN_SEG = ICP_EX_MIN_SEG; // model points per segment at least (4096; 1024 was measured slower: more tickets and merges)
 
 __global__ void __launch_bounds__(EXACT_THREADS)
 nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,

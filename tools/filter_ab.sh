@@ -5,7 +5,7 @@
 # The default build runs first AND last so that drift of the box shows.   usage: bash tools/filter_ab.sh [variants...]
 cd "${GRAFT_REPO_ROOT:-.}"
 mkdir -p gpurun_out
-V="${@:-u4 u8 g128 g128u4 g128u8 g256u8 r12c3 r12c3u4 r12c3g128u4 r12c3g128u8 r16c2 r16c2g128u4 rf4 rf16}"
+V="${@:-u4 u8 g128 g128u4 g128u8 g256u8 r12c3 r12c3u4 r12c3g128u4 r12c3g128u8 r16c2 r16c2g128u4 rf4 rf16 exseg2k exp8 exp2}"
 LIBDIR=$PWD/iterative-closest-point_b200/lib
 run() {   # name, library
   export ICP_B200_LIB=$2
