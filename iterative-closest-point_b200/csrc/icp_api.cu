@@ -111,6 +111,7 @@ struct icp_ctx {
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
     int forced_ctas = 0;
+    int min_units = 0;                     // ICP_NN_MIN_UNITS: least chunk-units per filter CTA (0 = one staged tile = 8)
     size_t cap_nm = 0, cap_np = 0;         // allocated capacities (points): buffers only ever grow
     // fused alignment kernel (cooperative) and the peer-memory exchange it carries when world > 1
     int align_blocks_max = 148;
@@ -235,7 +236,10 @@ void choose_splits(icp_ctx* c)
     if (waves < 1) waves = 1;
     long long n_cta = wave * waves;
     if (c->forced_ctas > 0) n_cta = c->forced_ctas;
-    if (n_cta > total / (NN_TM / NN_G)) n_cta = total / (NN_TM / NN_G);
+    // ICP_NN_MIN_UNITS (experiment): fewer chunks per CTA than one staged tile spreads a SMALL cloud over more SMs (cow:
+    // 144 chunk-units = 18 CTAs of 8 on a 148-SM GPU); the kernel then stages a whole tile for the chunks it needs.
+    const long long min_units = c->min_units > 0 ? c->min_units : NN_TM / NN_G;
+    if (n_cta > total / min_units) n_cta = total / min_units;
     if (n_cta < 1) n_cta = 1;
     c->sc.n_cta = (int)n_cta;
     c->sc.n_splits = (int)((n_cta + n_tiles - 1) / n_tiles + 1);
@@ -516,6 +520,7 @@ int icp_create(icp_ctx** out, int device)
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
     if (const char* e = getenv("ICP_NN_CTAS")) c->forced_ctas = atoi(e);
+    if (const char* e = getenv("ICP_NN_MIN_UNITS")) c->min_units = atoi(e);
     if ((r = set_identity_xf(c))) { delete c; return r; }
     *out = c;
     return ICP_OK;

@@ -18,6 +18,7 @@ NN_TILE, NN_G, NN_TM = 1024, 64, 512
 CPM = NN_TM // NN_G
 SMS = 148
 MIN_CTAS = 4          # resident filter CTAs per SM (NN_MIN_CTAS)
+MIN_UNITS = 0         # ICP_NN_MIN_UNITS: least chunk-units per CTA (0 = one staged tile)
 
 
 def pad(n, q):
@@ -35,7 +36,7 @@ def choose_splits(np_, nm, forced=0, sm_count=SMS):
     n_cta = wave * waves
     if forced > 0:
         n_cta = forced
-    n_cta = min(n_cta, total // CPM)
+    n_cta = min(n_cta, total // (MIN_UNITS if MIN_UNITS > 0 else CPM))
     n_cta = max(n_cta, 1)
     return n_cta, (n_cta + n_tiles - 1) // n_tiles + 1
 
@@ -134,3 +135,18 @@ def test_variant_geometries(monkeypatch, r, g, ctas):
         assert n_cta <= SMS * ctas or n_cta % (SMS * ctas) == 0
     for forced in (1, 3, 37, 444, 5000):
         check(5000, 4097, forced)
+
+
+@pytest.mark.parametrize("min_units", [1, 2, 4])
+def test_fine_decomposition_of_small_clouds(monkeypatch, min_units):
+    """ICP_NN_MIN_UNITS < 8: a CTA may own less than one staged model tile (cow: 144 chunk-units on up to 144 CTAs
+    instead of 18); ranges, slots and staged tiles must still be exactly what nn_refine expects."""
+    import sys
+    monkeypatch.setattr(sys.modules[__name__], "MIN_UNITS", min_units)
+    for np_ in (1, 1023, 1025, 2903, 5000, 9000):
+        for nm in (1, 64, 65, 513, 2903, 4097):
+            n_cta, n_splits = check(np_, nm)
+            for forced in (1, 7, 37, 593, 5000):
+                check(np_, nm, forced)
+    n_cta, n_splits = check(2903, 2903)
+    assert n_cta == 144 // min_units and n_splits == (n_cta + 2) // 3 + 1

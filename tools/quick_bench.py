@@ -41,6 +41,11 @@ def loop_timing(tag, m, p, max_iter=30, check=True):
 if __name__ == "__main__":
     cow_r, cow_1 = load("cow_ref"), load("cow_tr1")
     closest_timing("cow", cow_r, cow_1); loop_timing("cow", cow_r, cow_1)
+    if os.environ.get("QB_ONLY_SMALL"):          # small clouds only (ICP_NN_MIN_UNITS experiment)
+        for n in (8192, 16384):
+            m, p, _ = synthetic_pair(n, seed=n)
+            closest_timing(f"synthetic {n}", m, p); loop_timing(f"synthetic {n}", m, p, max_iter=10)
+        sys.exit(0)
     h_r, h_1 = load("horse_ref"), load("horse_tr1")
     closest_timing("horse", h_r, h_1); loop_timing("horse_tr1", h_r, h_1)
     for s in os.environ.get("QB_CTAS", "").split(","):

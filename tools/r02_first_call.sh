@@ -10,5 +10,12 @@ timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "r
 timeout 600 python bench.py > gpurun_out/bench_horse.json 2> gpurun_out/bench_horse.err
 timeout 600 python tools/graph_check.py > gpurun_out/graph_check.log 2>&1; echo "rc=$?" >> gpurun_out/graph_check.log
 ICP_PROFILE=1 timeout 600 python tools/quick_bench.py > gpurun_out/quick_profile.log 2>&1
+# small clouds: fewer chunk-units per filter CTA than one staged tile (cow: 18 CTAs -> up to 144); parity first, then the cow lines
+for u in 4 2 1; do
+  ICP_NN_MIN_UNITS=$u timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/minunits_${u}_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/minunits_${u}_pytest.log
+  ICP_NN_MIN_UNITS=$u QB_ONLY_SMALL=1 timeout 300 python tools/quick_bench.py > gpurun_out/minunits_${u}_quick.log 2>&1
+  ICP_NN_MIN_UNITS=$u timeout 300 python bench.py --skip-cpu-baseline --workload cow --steps 20 --warmup 3 > gpurun_out/minunits_${u}_cow.json 2> gpurun_out/minunits_${u}_cow.err
+done
+timeout 300 python bench.py --skip-cpu-baseline --workload cow --steps 20 --warmup 3 > gpurun_out/minunits_8_cow.json 2> gpurun_out/minunits_8_cow.err
 timeout 2400 bash tools/filter_ab.sh > gpurun_out/filter_ab.log 2>&1
-tail -3 gpurun_out/pytest_gpu.log; tail -1 gpurun_out/smoke.log; cat gpurun_out/graph_check.log; cat gpurun_out/ab_summary.txt
+tail -3 gpurun_out/pytest_gpu.log; tail -1 gpurun_out/smoke.log; cat gpurun_out/graph_check.log; head -3 gpurun_out/minunits_*_quick.log; tail -2 gpurun_out/minunits_*_pytest.log; cat gpurun_out/ab_summary.txt
