@@ -1,7 +1,7 @@
 #!/bin/bash
-# First gpurun call of the next round: regression (GPU tests, smoke, default bench) and the two experiments staged at
-# the end of round 1 without GPU time: ICP_GRAPH (tools/graph_check.py) and the filter's build-time variants
-# (tools/filter_ab.sh).  BEFORE the call, in the build container:  make -C iterative-closest-point_b200 variants
+# First gpurun call of the next round: regression (GPU tests, smoke, default bench) and the experiments staged at the
+# end of round 1 without GPU time: ICP_GRAPH (tools/graph_check.py), ICP_NN_MIN_UNITS (small clouds) and the build-time
+# variants of filter / refine / exact (tools/filter_ab.sh).  BEFORE the call, in the build container:  make -C iterative-closest-point_b200 variants
 #   gpurun --timeout 3000 -- 'bash tools/r02_first_call.sh'
 cd "${GRAFT_REPO_ROOT:-.}"
 mkdir -p gpurun_out
