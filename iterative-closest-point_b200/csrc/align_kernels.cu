@@ -97,7 +97,15 @@ __device__ void peer_allreduce(const PeerComm& pc, const double* vals, int n, do
 
 // ------------------------------------------------------------------------------------------------
 // K2: moments.
-__global__ void __launch_bounds__(RED_THREADS)
+// ICP_RED_MIN_CTAS (build-time variant, like ICP_NN_*): the kernel needs 126 registers because the Horn solve rides on
+// its last block, which leaves 2 CTAs per SM for the streaming loop; a bound of 4 trades spills in that tail (one
+// thread, once per launch) for twice the loads in flight on multi-million-point clouds.
+#ifdef ICP_RED_MIN_CTAS
+#define RED_BOUNDS __launch_bounds__(RED_THREADS, ICP_RED_MIN_CTAS)
+#else
+#define RED_BOUNDS __launch_bounds__(RED_THREADS)
+#endif
+__global__ void RED_BOUNDS
 moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
                const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
                const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
