@@ -503,10 +503,10 @@ int icp_create(icp_ctx** out, int device)
     if ((r = dalloc(&c->d_mom, MOM_N)) || (r = dalloc(&c->d_xf, XF_N)) || (r = dalloc(&c->d_err_sum, 1)) ||
         (r = dalloc(&c->d_out6, 8)) || (r = dalloc(&c->d_ctl, CTL_N)) || (r = dalloc(&c->m.geo, 16)) ||
         (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 18))) {
-        delete c;
+        icp_destroy(c);                       // frees whatever was allocated so far
         return r;
     }
-    if ((r = dalloc(&c->d_trace, 16))) { delete c; return r; }
+    if ((r = dalloc(&c->d_trace, 16))) { icp_destroy(c); return r; }
     CK(cudaMemset(c->d_trace, 0, 16 * sizeof(unsigned long long)));
     c->align_blocks_max = align_fused_max_blocks(c->sm_count);
     if (const char* e = getenv("ICP_COMM")) c->force_nccl = !strcmp(e, "nccl");
@@ -521,7 +521,7 @@ int icp_create(icp_ctx** out, int device)
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
     if (const char* e = getenv("ICP_NN_CTAS")) c->forced_ctas = atoi(e);
     if (const char* e = getenv("ICP_NN_MIN_UNITS")) c->min_units = atoi(e);
-    if ((r = set_identity_xf(c))) { delete c; return r; }
+    if ((r = set_identity_xf(c))) { icp_destroy(c); return r; }
     *out = c;
     return ICP_OK;
 }
@@ -595,7 +595,8 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
     const int64_t np_pad = (np + NN_TILE - 1) / NN_TILE * NN_TILE;
     c->s.np = np; c->s.np_pad = np_pad;
     if (c->cap_np < (size_t)np_pad) {            // grow only
-        c->cap_np = (size_t)np_pad;
+        c->cap_np = 0;                           // stays 0 (and the scene unset) if an allocation below fails
+        c->have_scene = false;
         if ((r = dalloc(&c->s.p64x, (size_t)np_pad)) || (r = dalloc(&c->s.p64y, (size_t)np_pad)) ||
             (r = dalloc(&c->s.p64z, (size_t)np_pad)) || (r = dalloc(&c->s.q64x, (size_t)np_pad)) ||
             (r = dalloc(&c->s.q64y, (size_t)np_pad)) || (r = dalloc(&c->s.q64z, (size_t)np_pad)) ||
@@ -611,6 +612,7 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
             (r = dalloc(&c->sc.batch_ticket, n_tickets)))
             return r;
         CK(cudaMemsetAsync(c->sc.batch_ticket, 0, n_tickets * sizeof(int), c->st));
+        c->cap_np = (size_t)np_pad;
     }
     // Morton sort of the scene (once per scene; a similarity transform keeps tiles compact)
     if ((r = ensure_sort(c, (size_t)np))) return r;
