@@ -361,10 +361,19 @@ int max_element_index_literal(const double ev[4])
     return index;
 }
 
+// libm's pow, reached through a volatile pointer: g++ folds pow(x, 2.0) with a visible constant exponent into x * x
+// (no call is left at -O1 and above), whereas the reference's Eigen expression array().pow(2) (src/cpu.cc:17) does
+// call libm's pow with a run-time exponent - 176 975 589 calls in benchmark/callgrind.out.76685 - and glibc's
+// pow(x, 2) differs from x * x by one ulp for ~0.08 % of inputs.  The literal mode must see that.
+double (*volatile g_libm_pow)(double, double) = ::pow;
+
 inline double dist_eval(int mode, double px, double py, double pz, double mx, double my, double mz)
 {
     double dx = px - mx, dy = py - my, dz = pz - mz;      // src/cpu.cc:16 (pi - mk)
-    if (mode == 0) return std::sqrt((std::pow(dx, 2.0) + std::pow(dy, 2.0)) + std::pow(dz, 2.0));  // :17-18
+    if (mode == 0) {                                      // :17-18
+        double (*const lp)(double, double) = g_libm_pow;
+        return std::sqrt((lp(dx, 2.0) + lp(dy, 2.0)) + lp(dz, 2.0));
+    }
     double s = (dx * dx + dy * dy) + dz * dz;
     return mode == 1 ? std::sqrt(s) : s;
 }

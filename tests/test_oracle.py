@@ -101,3 +101,31 @@ def test_synthetic_pair_has_known_correspondence():
     m, p, perm = synthetic_pair(2000, seed=3, angle_deg=0.05, noise=1e-4, shift=(0, 0, 0))
     idx, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
     assert (idx == perm).mean() > 0.99
+
+
+def test_literal_mode_really_calls_libm_pow(clouds):
+    """The reference's Eigen expression array().pow(2) (src/cpu.cc:17) calls libm's pow (callgrind: 176 975 589 calls),
+    and glibc's pow(x, 2) is not x*x for ~0.09 % of inputs.  g++ folds std::pow(x, 2.0) with a visible constant into
+    x*x, which would make the literal mode a copy of the mulsqrt mode and its 'no index mismatch' result vacuous: the
+    oracle (and the Eigen stand-in of oracle/_ref) therefore reach pow through a volatile pointer.  Checked here: the
+    library imports pow, pow(x, 2) does differ from x*x on this machine, and the two modes still pick the same model
+    point for every scene point of cow_tr2 (all 2 903) and of a 4 096-point sample of horse_tr1 x horse_ref.
+    tests/golden/check_literal_full.py holds the same comparison on the full large clouds (literal_full_check.json)."""
+    import ctypes
+    import json
+    import subprocess
+    so = os.path.join(os.path.dirname(O.__file__), "liboracle_icp.so")
+    O.lib()
+    assert " U pow" in subprocess.run(["nm", "-D", so], capture_output=True, text=True, check=True).stdout
+    libm = ctypes.CDLL("libm.so.6")
+    libm.pow.restype = ctypes.c_double
+    libm.pow.argtypes = [ctypes.c_double, ctypes.c_double]
+    x = np.random.default_rng(0).uniform(-1, 1, 20000)
+    assert sum(libm.pow(float(v), 2.0) != float(v) * float(v) for v in x) > 0
+    m, p = clouds("cow_ref"), clouds("cow_tr2")
+    assert np.array_equal(O.closest_matrix(p, m, O.NN_LITERAL)[0], O.closest_matrix(p, m, O.NN_MULSQRT)[0])
+    m, p = clouds("horse_ref"), clouds("horse_tr1")
+    sub = np.random.default_rng(1).choice(len(p), 4096, replace=False)
+    assert np.array_equal(O.closest_matrix(p[sub], m, O.NN_LITERAL)[0], O.closest_matrix(p[sub], m, O.NN_MULSQRT)[0])
+    full = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "literal_full_check.json")))
+    assert len(full) == 4 and all(v["index_mismatches"] == 0 for v in full.values())
