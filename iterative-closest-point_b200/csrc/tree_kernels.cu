@@ -22,6 +22,8 @@
 // icp_api.cu then keeps the brute-force path, whose bound has no such restriction.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdlib>
+
 #include "icp_common.cuh"
 
 namespace icpb {
@@ -677,7 +679,17 @@ void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int
                                                     use_prev, ctl, honor_done, progress);
 }
 
-int kd_global_min_points() { return KD_GLOBAL_MIN_POINTS; }
+// ICP_KD_GLOBAL_MIN (experiment): the CPU emulation gives horse 4.70 -> 3.79 leaves per search with the global levels
+// switched on below 131 072 points (tools/tree_order_emul.py); whether the costlier build pays is a GPU question.
+int kd_global_min_points()
+{
+    static const int v = [] {
+        const char* e = getenv("ICP_KD_GLOBAL_MIN");
+        const int x = e ? atoi(e) : 0;
+        return x >= 2 * KD_B ? x : KD_GLOBAL_MIN_POINTS;
+    }();
+    return v;
+}
 
 size_t tree_sort_bytes(int n)
 {

@@ -17,5 +17,11 @@ for u in 4 2 1; do
   ICP_NN_MIN_UNITS=$u timeout 300 python bench.py --skip-cpu-baseline --workload cow --steps 20 --warmup 3 > gpurun_out/minunits_${u}_cow.json 2> gpurun_out/minunits_${u}_cow.err
 done
 timeout 300 python bench.py --skip-cpu-baseline --workload cow --steps 20 --warmup 3 > gpurun_out/minunits_8_cow.json 2> gpurun_out/minunits_8_cow.err
+# tree search: global k-d levels also for models below 131 072 points (emulation: horse 4.70 -> 3.79 leaves per search)
+ICP_KD_GLOBAL_MIN=16384 timeout 900 python -m pytest tests/test_gpu_tree.py -m gpu -x -q > gpurun_out/kdmin_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/kdmin_pytest.log
+for w in horse horse_tr2 bunny syn64k; do
+  timeout 300 python bench.py --nn tree --skip-cpu-baseline --workload $w --steps 10 --warmup 3 > gpurun_out/kdmin_default_$w.json 2>/dev/null
+  ICP_KD_GLOBAL_MIN=16384 timeout 300 python bench.py --nn tree --skip-cpu-baseline --workload $w --steps 10 --warmup 3 > gpurun_out/kdmin_16k_$w.json 2>/dev/null
+done
 timeout 2400 bash tools/filter_ab.sh > gpurun_out/filter_ab.log 2>&1
-tail -3 gpurun_out/pytest_gpu.log; tail -1 gpurun_out/smoke.log; cat gpurun_out/graph_check.log; head -3 gpurun_out/minunits_*_quick.log; tail -2 gpurun_out/minunits_*_pytest.log; cat gpurun_out/ab_summary.txt
+tail -3 gpurun_out/pytest_gpu.log; tail -1 gpurun_out/smoke.log; cat gpurun_out/graph_check.log; head -3 gpurun_out/minunits_*_quick.log; tail -2 gpurun_out/minunits_*_pytest.log gpurun_out/kdmin_pytest.log; grep -ho '"ms_per_step": [0-9.]*' gpurun_out/kdmin_*.json | paste - - ; cat gpurun_out/ab_summary.txt
