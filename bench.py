@@ -3,21 +3,24 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
 
-A *step* is one full find_corresponding loop (reference src/cpu.cc:55-79) over one cloud pair.
-Default workload = BASELINE.json configs[1]: horse_ref vs horse_tr1, max_iter 30 (48 485 x 48 485 points,
-runs all 30 iterations).  metric = nearest-neighbour distance evaluations per second (np*nm per
-iteration); ICP iterations/s is reported next to it.
+A *step* is one find_corresponding loop (reference src/cpu.cc:55-79) over one cloud pair.
+Default workload = north_star's own target, BASELINE.json configs[3]: the synthetic 2^22 x 2^22 cloud pair of
+SURVEY §8d (splitmix64 / Box-Muller recipe, icp_b200/synth.py), exact brute force, max_iter 2 per step, **strong
+scaling**: the ONE scene is cut into N contiguous blocks (rank r holds block r), the model is replicated — the
+reference's own answer to "more points" is the slab loop of src/GPU/compute.cu:156-235.  The round-1 headline
+(configs[1], horse_ref x horse_tr1, 30 iterations) is measured in the same run and reported under `secondary.horse`.
+metric = nearest-neighbour distance evaluations per second (np*nm per iteration); ICP iterations/s next to it.
 
   value     device-timed (CUDA events on the library's stream), clouds already resident in HBM
-  e2e       same loop through the C-ABI with HOST buffers: set_model + set_scene (H2D, Morton sort),
+  e2e       same loop through the C-ABI with pinned HOST buffers: set_model + set_scene (H2D, Morton sort),
             run, get_scene (D2H) inside the timed region, wall clock
   roofline  the FP32 filter kernel (nn_filter_kernel): 8 algorithmic flops per evaluation against the
             FP32 FMA peak  SMs x 128 lanes x 2 x f_max
+  parity    N > 1 only: BEFORE timing, the communicator that will be timed runs horse_ref x horse_tr2 cut into N blocks
+            and must reproduce the golden vectors (iteration count, error history 1e-5, per-shard indices bit-exact,
+            bit-identical transform on every rank); a failure exits non-zero.
   cpu_baseline / --impl reference : the CPU oracle (restatement of the reference's cpu.cc; the reference
             itself needs Eigen, which is not installed) timed on the host cores on a bounded sample.
-
-N > 1 (torchrun): the scene is N horse-sized shards (rank r holds one), the model is replicated, the
-18 moment sums and the residual are all-reduced through NCCL every iteration -> weak scaling.
 """
 import argparse
 import json
@@ -41,6 +44,8 @@ WORKLOADS = {   # name -> (model cloud, scene cloud, max_iter, check_sizes)
     "bunny": ("bun000", "bun045", 30, False),
 }
 SYNTHETIC = {"syn64k": 1 << 16, "syn256k": 1 << 18, "syn1m": 1 << 20, "syn2m": 1 << 21, "syn4m": 1 << 22}
+SYN_ITERS = {"syn64k": 10, "syn256k": 10, "syn1m": 2, "syn2m": 2, "syn4m": 2}      # iterations per step (fixed)
+DEFAULT_WORKLOAD = "syn4m"
 
 
 def load_cloud(name):
@@ -50,37 +55,27 @@ def load_cloud(name):
     return np.array([[float(x) for x in l.split(",")[:3]] for l in lines], dtype=np.float64)
 
 
-def synthetic(n, seed, angle_deg=5.0):
-    """model ~ U[-1,1]^3, scene = R m + t + 1e-3 noise, pseudo-randomly permuted."""
-    rng = np.random.default_rng(seed)
-    m = rng.uniform(-1.0, 1.0, (n, 3))
-    ax = np.array([1.0, 2.0, 3.0]) / np.sqrt(14.0)
-    a = np.deg2rad(angle_deg)
-    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
-    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
-    p = m @ R.T + np.array([0.05, -0.03, 0.02]) + 1e-3 * rng.standard_normal((n, 3))
-    return m, np.ascontiguousarray(p[rng.permutation(n)])
-
-
 def get_workload(name, max_iter=None):
     m, p, it, chk, desc = _get_workload(name)
     if max_iter:
         it = max_iter
-        desc = desc.split(", max_iter")[0].split(", 10 iterations")[0] + f", max_iter {it}"
+        desc = desc.split(", max_iter")[0] + f", max_iter {it}"
     return m, p, it, chk, desc
 
 
 def _get_workload(name):
+    from icp_b200 import synth
     if name in WORKLOADS:
         mn, pn, it, chk = WORKLOADS[name]
         return load_cloud(mn), load_cloud(pn), it, chk, f"{mn} vs {pn}, max_iter {it}"
     if name.startswith("batch"):     # reference arm / CPU baseline of the batched workload: its first pair
         n = {"batch64k": 1 << 16, "batch16k": 1 << 14}[name]
-        m, p = synthetic(n, 1000, angle_deg=2.0)
-        return m, p, 30, True, f"first pair of the batch: synthetic {n} points, rigid 2deg + 1e-3 noise, max_iter 30"
+        m, p = synth.config5_pair(0, n)
+        return m, p, 30, True, f"first pair of the batch: synthetic {n} points (SURVEY 8d config 5), max_iter 30"
     n = SYNTHETIC[name]
-    m, p = synthetic(n, 1000 + int(np.log2(n)))
-    return m, p, 10, True, f"synthetic 2^{int(np.log2(n))} points, rigid 5deg + 1e-3 noise, 10 iterations"
+    m, p = synth.config4(n)
+    return m, p, SYN_ITERS[name], True, (f"synthetic 2^{int(np.log2(n))} x 2^{int(np.log2(n))} points (SURVEY 8d config 4: splitmix64 "
+                                         f"model, rigid 5deg + 1e-3 Box-Muller noise, permuted), max_iter {SYN_ITERS[name]}")
 
 
 class ClockSampler:
@@ -129,6 +124,18 @@ def fp32_peak_tflops():
     return 148 * 128 * 2 * mhz * 1e6 / 1e12, src
 
 
+def filter_traffic(workload, nn):
+    """dram__bytes_read + dram__bytes_write of ONE nn_filter_kernel launch from a committed `ncu --set full` capture of this
+    workload (profiles/nn_filter_traffic.json: {"workloads": {name: bytes}}); None where no capture covers the workload."""
+    if nn != "brute":
+        return None
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "nn_filter_traffic.json")))
+        return t.get("workloads", {}).get(workload)
+    except Exception:
+        return None
+
+
 def host_threads():
     """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1, which is not what we want)."""
     try:
@@ -170,43 +177,215 @@ def ref_source_throughput(m, p, max_pairs=2.0e7):
         return {"error": str(e)}
 
 
+NN_DESC = {"brute": "exact brute force (every pair evaluated)",
+           "tree": "exact bounding-box hierarchy (ICP_NN_TREE): identical indices; evals/s counts the np*nm pairs a brute-force "
+                   "search would evaluate, not executed work - compare icp_iterations_per_sec"}
+L2_NOTE = "flushed between steps (256 MB write)"
+
+
+def workload_config(args, m, p_global_n, max_iter, desc):
+    """`config` of the JSON line: what is measured, the same in both arms (sharding and launch geometry go under `layout`)."""
+    return {"workload": args.workload, "description": desc, "np": int(p_global_n), "nm": int(len(m)), "max_iter": int(max_iter),
+            "nn": NN_DESC[args.nn], "l2": L2_NOTE}
+
+
+def cpu_sample(m, p, max_iter):
+    """Bounded CPU sample of a workload: (scene sample, iterations, description)."""
+    if len(m) * len(p) > 1e11:          # synthetic >= 2^20: 4096 scene points against the full model, one iteration
+        return p[:4096], 1, "4096-point scene sample"
+    if len(m) * len(p) > 1e9:
+        return p, min(2, max_iter), "full clouds"
+    return p, max_iter, "full clouds"
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU path (oracle port; Eigen is absent so cpu.cc cannot be
     compiled) on the host cores, all threads, on a bounded sample of the same workload."""
     if rank != 0:
         return
     m, p, max_iter, _, desc = get_workload(args.workload, args.max_iter)
-    sample_iters = 2 if len(m) * len(p) > 1e9 else max_iter
-    if len(m) * len(p) > 1e11:      # synthetic >= 2^20: sample 4096 scene points against the full model
-        p = p[:4096]
-        sample_iters = 1
+    ps, sample_iters, what = cpu_sample(m, p, max_iter)
     vals = []
     for i in range(args.warmup + args.steps):
-        v, it, dt, cores = cpu_port_throughput(m, p, sample_iters, threads=host_threads())
+        v, it, dt, cores = cpu_port_throughput(m, ps, sample_iters, threads=host_threads())
         if i >= args.warmup:
             vals.append((v, it, dt))
     value = float(np.mean([v for v, _, _ in vals]))
     ms = float(np.mean([dt for _, _, dt in vals])) * 1e3
-    sample = f"{vals[-1][1]} ICP iteration(s) of {desc} ({len(p)} scene x {len(m)} model points) per step"
+    sample = f"{vals[-1][1]} ICP iteration(s) per step, {what} ({len(ps)} scene x {len(m)} model points), oracle x*x+sqrt form, OpenMP"
     line = {"impl": "reference", "metric": "nn_distance_evals_per_sec", "value": value, "unit": "evals/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "reference clouds",
-            "icp_iterations_per_sec": float(np.mean([it / dt for _, it, dt in vals])),
-            "config": {"workload": args.workload, "description": desc},
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
+            "data": "reference clouds (tests/golden/clouds)" if args.workload in WORKLOADS else "synthetic",
+            "icp_iterations_per_sec": float(np.mean([it / dt for _, it, dt in vals])) * (len(ps) / len(p)),
+            "config": workload_config(args, m, len(p), max_iter, desc),
             "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample,
                              "reference_source": ref_source_throughput(m, p)},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
-NN_DESC = {"brute": "exact brute force (every pair evaluated)",
-           "tree": "exact bounding-box hierarchy (ICP_NN_TREE): identical indices; evals/s counts the np*nm pairs a brute-force "
-                   "search would evaluate, not executed work - compare icp_iterations_per_sec"}
+# ---- the GPU arm ---------------------------------------------------------------------------------------------
+
+class Harness:
+    """One context per rank (+ communicator when world > 1) and the timing helpers shared by the main and secondary lines."""
+
+    def __init__(self, args, rank, world, local_rank, torch, dist):
+        import icp_b200
+        self.icp, self.args, self.rank, self.world, self.local, self.torch, self.dist = icp_b200, args, rank, world, local_rank, torch, dist
+        self.ctx = icp_b200.Context(local_rank)
+        self.comm_kind = "none"
+        if world > 1:
+            uid = [icp_b200.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            self.ctx.comm_init(uid[0], rank, world)
+            self.comm_kind = "nccl all-reduce of 18+1 doubles per iteration"
+            if os.environ.get("ICP_COMM", "peer") != "nccl":
+                handles = [None] * world
+                dist.all_gather_object(handles, self.ctx.comm_peer_handle())
+                self.ctx.comm_peer_attach(handles, rank, world)
+                dist.barrier()
+                self.comm_kind = "in-kernel peer-mailbox exchange of 18+1 doubles per iteration over NVLink (no collective launch)"
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.dist:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce_max(self, vals):
+        t = self.torch.tensor(vals, dtype=self.torch.float64, device="cuda")
+        if self.dist:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.tolist()
+
+    def shard(self, p, scaling):
+        """-> (this rank's scene block, global scene size)."""
+        if self.world > 1 and scaling == "strong":
+            lo, hi = self.icp.shard_range(len(p), self.rank, self.world)
+            return np.ascontiguousarray(p[lo:hi]), len(p)
+        return p, len(p) * self.world
+
+    def parity_gate(self):
+        """horse_ref x horse_tr2 (8 iterations, the knife-edge threshold case) cut into `world` blocks, on the
+        communicator that is about to be timed, against tests/golden/horse_tr2.npz.  Loop being sharded: src/cpu.cc:55-79."""
+        torch, dist, ctx = self.torch, self.dist, self.ctx
+        m, p = load_cloud("horse_ref"), load_cloud("horse_tr2")
+        g = np.load(os.path.join(ROOT, "tests", "golden", "horse_tr2.npz"))
+        lo, hi = self.icp.shard_range(len(p), self.rank, self.world)
+        ctx.set_model(m)
+        ctx.set_scene(p[lo:hi])
+        it, hist = ctx.run(30, 1e-5, True)
+        idx, new_p = ctx.indices(), ctx.get_scene()
+        s, R, t = ctx.transform()
+        checks = [it == int(g["iters"]),
+                  len(hist) == int(g["iters"]) and bool(np.allclose(hist, g["err"][:it], rtol=1e-5, atol=1e-18)),
+                  bool(np.array_equal(idx, g["idx_last"][lo:hi])),
+                  bool(np.abs(new_p - g["new_p"][lo:hi]).max() < 1e-9),
+                  bool(np.allclose(R, g["R"][-1], rtol=1e-5, atol=1e-9) and abs(s - g["s"][-1]) <= 1e-5 * abs(g["s"][-1]))]
+        flags = torch.tensor([int(c) for c in checks], device="cuda")
+        xf = torch.tensor(np.concatenate([[s], R.ravel(), t, hist]), device="cuda")
+        lo_xf, hi_xf = xf.clone(), xf.clone()
+        if dist:
+            dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+            dist.all_reduce(lo_xf, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi_xf, op=dist.ReduceOp.MAX)
+        same = bool(torch.equal(lo_xf, hi_xf))
+        f = [bool(x) for x in flags.tolist()]
+        return {"case": "horse_tr2", "world": self.world, "ok": all(f) and same, "iterations": it, "golden_iterations": int(g["iters"]),
+                "iteration_count": f[0], "error_history_1e-5": f[1], "indices_bit_exact_per_shard": f[2], "new_p_1e-9": f[3],
+                "s_R_1e-5": f[4], "transform_and_history_bit_identical_on_all_ranks": same,
+                "exchange": os.environ.get("ICP_COMM", "peer"), "nn": self.args.nn}
+
+    def timed_loop(self, m, p_shard, max_iter, check, steps, warmup, sample_clocks):
+        """Device-timed steps with the clouds resident.  -> dict (times are this rank's; reduce with reduce_max)."""
+        ctx, torch = self.ctx, self.torch
+        ctx.set_model(m)
+        ctx.set_scene(p_shard)
+
+        def step():
+            self.flush.fill_(1)                  # flush L2 between timed iterations
+            torch.cuda.synchronize()
+            ctx.reset_scene()
+            it, hist = ctx.run(max_iter, 1e-5, check)
+            return it, hist, ctx.stats()
+
+        for _ in range(max(warmup, 3)):
+            it, hist, st = step()
+        self.barrier()
+        sampler = ClockSampler(self.local) if (sample_clocks and self.rank == 0) else None
+        t_begin = time.perf_counter()
+        dev_ms = filt_ms = 0.0
+        launches = iters_total = 0
+        for _ in range(steps):
+            it, hist, st = step()
+            dev_ms += st["ms_total"]
+            filt_ms += st["ms_filter"]
+            launches += st["kernels_launched"] + 1     # + scene restore
+            iters_total += it
+        self.barrier()
+        t_end = time.perf_counter()
+        clocks = sampler.stop(t_begin, t_end) if sampler else None
+        return {"dev_ms": dev_ms, "filt_ms": filt_ms, "launches": launches, "iters_total": iters_total, "hist": hist, "st": st,
+                "clocks": clocks, "wall_s": t_end - t_begin}
+
+    def e2e_loop(self, m, p_shard, max_iter, check, reps):
+        """The same loop through the C-ABI with page-locked HOST buffers, wall clock.  -> (seconds per step, iterations, kind)."""
+        ctx, torch = self.ctx, self.torch
+        host_kind = "pinned"
+        try:
+            keep = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in (m, p_shard)]
+            keep.append(torch.empty((len(p_shard), 3), dtype=torch.float64).pin_memory())
+            m_h, p_h, out_h = (t.numpy() for t in keep)
+        except Exception as e:                     # noqa: BLE001 - any failure: fall back, never lose the bench line
+            sys.stderr.write(f"[bench] pinning host buffers failed ({e}); e2e uses pageable memory\n")
+            m_h, p_h, out_h, host_kind = m, p_shard, None, "pageable"
+        ts, it2 = [], 0
+        for i in range(1 + reps):
+            self.barrier()
+            t0 = time.perf_counter()
+            ctx.set_model(m_h)
+            ctx.set_scene(p_h)
+            it2, _ = ctx.run(max_iter, 1e-5, check)
+            ctx.get_scene(out_h)
+            torch.cuda.synchronize()
+            ts.append(time.perf_counter() - t0)
+        return float(np.mean(ts[1:])), it2, host_kind
+
+    def measure(self, workload, m, p, max_iter, check, steps, warmup, e2e_reps, scaling, sample_clocks):
+        """One workload at this world size -> dict of the reduced numbers (valid on every rank)."""
+        p_shard, p_global_n = self.shard(p, scaling)
+        # the reference's size check (src/cpu.cc:42-53) is on the GLOBAL scene (the library sums np over the communicator);
+        # the weak form's N copies of the scene cannot pass it
+        check = check and (self.world == 1 or scaling == "strong")
+        r = self.timed_loop(m, p_shard, max_iter, check, steps, warmup, sample_clocks)
+        e2e_s, it2, host_kind = self.e2e_loop(m, p_shard, max_iter, check, e2e_reps)
+        dev_ms, e2e_s, filt_ms = self.reduce_max([r["dev_ms"], e2e_s, r["filt_ms"]])
+        pairs_per_iter = len(m) * p_global_n
+        iters_per_step = r["iters_total"] / steps
+        evals = pairs_per_iter * iters_per_step
+        ms_per_step = dev_ms / steps
+        peak, peak_src = fp32_peak_tflops()
+        filt_ms_per_launch = filt_ms / max(r["iters_total"], 1)
+        achieved = 8.0 * len(m) * len(p_shard) / (filt_ms_per_launch * 1e-3) / 1e12
+        roofline = None
+        if self.args.nn != "tree":
+            roofline = {"bound": "fp32", "kernel": "nn_filter_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                        "frac": achieved / peak, "peak_source": peak_src, "algorithmic_flops_per_eval": 8,
+                        "evals_per_launch": len(m) * len(p_shard), "avg_launch_ms": filt_ms_per_launch,
+                        "traffic": filter_traffic(workload, self.args.nn) if self.world == 1 else None}
+        return {"value": evals / (ms_per_step * 1e-3), "ms_per_step": ms_per_step, "iters_per_step": iters_per_step,
+                "evals": evals, "roofline": roofline, "np_per_gpu": len(p_shard), "p_global_n": p_global_n,
+                "e2e": {"value": evals / e2e_s, "unit": "evals/s", "ms_per_step": e2e_s * 1e3,
+                        "h2d_bytes_per_step": (len(m) + len(p_shard)) * 24, "d2h_bytes_per_step": len(p_shard) * 24 + it2 * 8 + 64,
+                        "host_buffers": host_kind, "steps": e2e_reps},
+                "launches": r["launches"], "clocks": r["clocks"], "hist": r["hist"], "st": r["st"],
+                "wall_ms_per_step_incl_flush": r["wall_s"] * 1e3 / steps}
 
 
 def run_ours(args, rank, world, local_rank):
     import torch
-    import icp_b200
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -217,142 +396,73 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     if args.workload.startswith('batch'):
         return run_batch(args, rank, world, local_rank, torch, dist)
+    H = Harness(args, rank, world, local_rank, torch, dist)
+
+    # ---- parity gate (N > 1): before anything is timed ------------------------------------------------------
+    parity = None
+    if world > 1 and not args.skip_parity:
+        parity = H.parity_gate()
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"parity": parity, "error": "sharded parity check failed; nothing was timed"}), flush=True)
+            dist.destroy_process_group()
+            sys.exit(1)
+
     m, p, max_iter, check, desc = get_workload(args.workload, args.max_iter)
-    if world > 1:
-        check = False        # global scene = `world` shards of np points; the model stays nm points
+    big = len(m) * len(p) > 1e12
+    e2e_reps = max(1, min(args.steps, 3 if big else 10))
+    R = H.measure(args.workload, m, p, max_iter, check, args.steps, args.warmup, e2e_reps, args.scaling, True)
 
-    if world > 1 and args.scaling == "strong":      # one global scene, contiguous block per rank
-        lo, hi = icp_b200.shard_range(len(p), rank, world)
-        p_global_n = len(p)
-        p = np.ascontiguousarray(p[lo:hi])
-    else:
-        p_global_n = len(p) * world
-    ctx = icp_b200.Context(local_rank)
-    comm_kind = "none"
-    if world > 1:
-        uid = [icp_b200.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        ctx.comm_init(uid[0], rank, world)
-        comm_kind = "nccl all-reduce of 18+1 doubles per iteration"
-        if os.environ.get("ICP_COMM", "peer") != "nccl":
-            handles = [None] * world
-            dist.all_gather_object(handles, ctx.comm_peer_handle())
-            ctx.comm_peer_attach(handles, rank, world)
-            dist.barrier()
-            comm_kind = "in-kernel peer-mailbox exchange of 18+1 doubles per iteration over NVLink (no collective launch)"
-    ctx.set_model(m)
-    ctx.set_scene(p)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def step():
-        flush.fill_(1)                       # flush L2 between timed iterations
-        torch.cuda.synchronize()
-        ctx.reset_scene()
-        it, hist = ctx.run(max_iter, 1e-5, check)
-        st = ctx.stats()
-        return it, hist, st
-
-    for _ in range(max(args.warmup, 3)):
-        it, hist, st = step()
-    barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    t_begin = time.perf_counter()
-    dev_ms = filt_ms = 0.0
-    launches = iters_total = 0
-    for _ in range(args.steps):
-        it, hist, st = step()
-        dev_ms += st["ms_total"]
-        filt_ms += st["ms_filter"]
-        launches += st["kernels_launched"] + 1     # + scene restore
-        iters_total += it
-    barrier()
-    t_end = time.perf_counter()
-    clocks = sampler.stop(t_begin, t_end) if sampler else None
-
-    # ---- end to end through the C-ABI with host buffers --------------------------------------------
-    # Host buffers in page-locked memory, as the contract asks (inputs copied from pinned host memory, the result read
-    # back into a pinned buffer); if pinning fails the pageable arrays are used and the line says so.
-    ctx2 = ctx
-    host_kind = "pinned"
-    try:
-        keep = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in (m, p)]
-        keep.append(torch.empty((len(p), 3), dtype=torch.float64).pin_memory())
-        m_h, p_h, out_h = (t.numpy() for t in keep)
-    except Exception as e:                     # noqa: BLE001 - any failure: fall back, never lose the bench line
-        sys.stderr.write(f"[bench] pinning host buffers failed ({e}); e2e uses pageable memory\n")
-        m_h, p_h, out_h, host_kind = m, p, None, "pageable"
-    e2e_t = []
-    e2e_reps = min(args.steps, 10)
-    for i in range(2 + e2e_reps):
-        barrier()
-        t0 = time.perf_counter()
-        ctx2.set_model(m_h)
-        ctx2.set_scene(p_h)
-        it2, hist2 = ctx2.run(max_iter, 1e-5, check)
-        out = ctx2.get_scene(out_h)
-        torch.cuda.synchronize()
-        e2e_t.append(time.perf_counter() - t0)
-    e2e_s = float(np.mean(e2e_t[2:]))
-
-    tim = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
-    if dist:
-        dist.all_reduce(tim, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_s = tim.tolist()
+    # ---- secondary: the round-1 headline (configs[1]) in the same run ---------------------------------------
+    secondary = None
+    if args.workload == DEFAULT_WORKLOAD and not args.no_secondary:
+        hm, hp, hit, hchk, hdesc = get_workload("horse")
+        secondary = {}
+        forms = [("horse", "strong")] if world == 1 else [("horse_strong", "strong"), ("horse_weak", "weak")]
+        for key, sc in forms:
+            S = H.measure("horse", hm, hp, hit, hchk, 10, 3, 5, sc, False)
+            secondary[key] = {"value": S["value"], "unit": "evals/s", "ms_per_step": S["ms_per_step"], "steps": 10,
+                              "iterations_per_step": S["iters_per_step"], "e2e": S["e2e"]["value"],
+                              "e2e_ms_per_step": S["e2e"]["ms_per_step"], "roofline_frac": S["roofline"]["frac"] if S["roofline"] else None,
+                              "filter_avg_launch_ms": S["roofline"]["avg_launch_ms"] if S["roofline"] else None,
+                              "np_per_gpu": S["np_per_gpu"], "scaling": sc if world > 1 else None, "description": hdesc +
+                              ("" if world == 1 else (": the one scene cut into N blocks" if sc == "strong" else
+                                                      ": every rank holds a full COPY of the scene (kernel-scaling probe, not a sharded scene)"))}
     if rank != 0:
         if dist:
             dist.destroy_process_group()
         return
 
-    pairs_per_iter = len(m) * p_global_n
-    evals = pairs_per_iter * (iters_total / args.steps)
-    ms_per_step = dev_ms / args.steps
-    value = evals / (ms_per_step * 1e-3)
-    peak, peak_src = fp32_peak_tflops()
-    filt_ms_per_launch = filt_ms / max(iters_total, 1)
-    achieved = 8.0 * len(m) * len(p) / (filt_ms_per_launch * 1e-3) / 1e12
-    traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "nn_filter_traffic.json")))
-    except Exception:
-        pass
     cpu = None
     if world == 1 and not args.skip_cpu_baseline:      # the CPU baseline is reported at N = 1 only
-        cpu_iters = 8 if len(m) * len(p) < 5e9 else 1
-        pc = p if len(m) * len(p) < 1e11 else p[:4096]
-        cv, cit, cdt, cores = cpu_port_throughput(m, pc, cpu_iters, threads=host_threads())
+        ps, cpu_iters, what = cpu_sample(m, p, min(max_iter, 8))
+        cv, cit, cdt, cores = cpu_port_throughput(m, ps, cpu_iters, threads=host_threads())
         cpu = {"value": cv, "unit": "evals/s", "cores": cores, "kind": "port",
-               "sample": f"{cit} ICP iteration(s), {len(pc)} scene x {len(m)} model points, oracle x*x+sqrt form",
+               "sample": f"{cit} ICP iteration(s), {what} ({len(ps)} scene x {len(m)} model points), oracle x*x+sqrt form, OpenMP",
                "reference_source": ref_source_throughput(m, p)}
+    st = R["st"]
     line = {
-        "metric": "nn_distance_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
-        "scaling": args.scaling if world > 1 else "weak",
+        "metric": "nn_distance_evals_per_sec", "value": R["value"], "unit": "evals/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": R["ms_per_step"], "higher_is_better": True,
+        "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f32 filter + f64 re-rank/alignment",
         "data": "reference clouds (tests/golden/clouds)" if args.workload in WORKLOADS else "synthetic",
-        "icp_iterations_per_sec": (iters_total / args.steps) / (ms_per_step * 1e-3),
-        "iterations_per_step": iters_total / args.steps, "final_error_value": float(hist[-1]),
-        "config": {"workload": args.workload, "description": desc, "np_per_gpu": len(p), "nm": len(m),
-                   "sharding": "1 GPU" if world == 1 else f"scene = {world} shards of ~{len(p)} points "
-                   f"({p_global_n} in total), model replicated, {comm_kind}",
-                   "l2": "flushed between steps (256 MB write)", "model_splits": st["n_splits"], "nn": NN_DESC[args.nn]},
-        "roofline": None if args.nn == "tree" else {"bound": "fp32", "kernel": "nn_filter_kernel", "achieved": achieved, "peak": peak,
-                     "unit": "TFLOP/s", "frac": achieved / peak, "peak_source": peak_src,
-                     "algorithmic_flops_per_eval": 8, "evals_per_launch": len(m) * len(p),
-                     "avg_launch_ms": filt_ms_per_launch,
-                     "traffic": traffic["dram_bytes_per_launch"] if traffic else None},
+        "icp_iterations_per_sec": R["iters_per_step"] / (R["ms_per_step"] * 1e-3),
+        "iterations_per_step": R["iters_per_step"], "final_error_value": float(R["hist"][-1]),
+        "config": workload_config(args, m, R["p_global_n"], max_iter, desc),
+        "layout": {"np_per_gpu": R["np_per_gpu"],
+                   "sharding": "1 GPU" if world == 1 else (
+                       f"scene of {R['p_global_n']} points cut into {world} contiguous blocks of ~{R['np_per_gpu']}" if args.scaling == "strong"
+                       else f"every rank holds a full copy of the scene as its shard ({R['p_global_n']} points in total)") +
+                   ("" if world == 1 else f", model replicated, {H.comm_kind}"),
+                   "model_splits": st["n_splits"]},
+        "roofline": R["roofline"],
         "cpu_baseline": cpu,
-        "e2e": {"value": evals / e2e_s, "unit": "evals/s", "ms_per_step": e2e_s * 1e3,
-                "h2d_bytes_per_step": (len(m) + len(p)) * 24, "d2h_bytes_per_step": len(p) * 24 + it2 * 8 + 64,
-                "host_buffers": host_kind},
-        "gpu_launches": launches, "clocks": clocks,
-        "rerank": {"full_fp64_scans_per_pass": st["rerank_full"] / max(st["nn_calls"], 1), "scene_points": len(p)},
-        "wall_ms_per_step_incl_flush": (t_end - t_begin) * 1e3 / args.steps,
+        "e2e": R["e2e"],
+        "gpu_launches": R["launches"], "clocks": R["clocks"],
+        "rerank": {"full_fp64_scans_per_pass": st["rerank_full"] / max(st["nn_calls"], 1), "scene_points": R["np_per_gpu"]},
+        "wall_ms_per_step_incl_flush": R["wall_ms_per_step_incl_flush"],
+        "parity": parity, "secondary": secondary,
     }
     print(json.dumps(line), flush=True)
     if dist:
@@ -364,12 +474,13 @@ def run_batch(args, rank, world, local_rank, torch, dist):
     exchanged); on each GPU `lanes` contexts run concurrently (icp_batch_run).  A step registers every pair once,
     through the C-ABI with HOST buffers (the batch entry point has no device-resident form), so value == e2e."""
     import icp_b200
+    from icp_b200 import synth
     n = {"batch64k": 1 << 16, "batch16k": 1 << 14}[args.workload]
     max_iter = args.max_iter or 30
     mine = list(range(rank, args.pairs, world))
     models, scenes = [], []
     for k in mine:
-        m, p = synthetic(n, 1000 + k, angle_deg=2.0 + 6.0 * ((k * 37) % 101) / 100.0)
+        m, p = synth.config5_pair(k, n)
         models.append(m)
         scenes.append(p)
 
@@ -387,8 +498,10 @@ def run_batch(args, rank, world, local_rank, torch, dist):
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     t0 = time.perf_counter()
+    launches = 0
     for _ in range(args.steps):
         res = step()
+        launches += int(res.get("kernels_launched", 0))
     torch.cuda.synchronize()
     dt_local = time.perf_counter() - t0
     barrier()
@@ -396,13 +509,18 @@ def run_batch(args, rank, world, local_rank, torch, dist):
     clocks = sampler.stop(t0, t1) if sampler else None
     evals_local = float(np.sum(res["iters"].astype(np.float64))) * n * n
     tim = torch.tensor([dt_local], dtype=torch.float64, device="cuda")
-    tot = torch.tensor([evals_local, float(np.sum(res["iters"]))], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([evals_local, float(np.sum(res["iters"])), float(launches)], dtype=torch.float64, device="cuda")
     if dist:
         dist.all_reduce(tim, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     if rank == 0:
         sec = tim.item() / args.steps
-        evals, iters = tot.tolist()
+        evals, iters, launches_all = tot.tolist()
+        cpu = None
+        if world == 1 and not args.skip_cpu_baseline:       # the port on the batch's first pair, two iterations
+            cv, cit, cdt, cores = cpu_port_throughput(models[0], scenes[0], 2, threads=host_threads())
+            cpu = {"value": cv, "unit": "evals/s", "cores": cores, "kind": "port",
+                   "sample": f"{cit} ICP iterations of pair 0 ({n} x {n} points), oracle x*x+sqrt form, OpenMP"}
         line = {"metric": "nn_distance_evals_per_sec", "value": evals / sec, "unit": "evals/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": sec * 1e3, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32 filter + f64 re-rank/alignment", "data": "synthetic",
@@ -410,10 +528,10 @@ def run_batch(args, rank, world, local_rank, torch, dist):
                 "config": {"workload": args.workload, "pairs": args.pairs, "points_per_cloud": n, "max_iter": max_iter,
                            "lanes_per_gpu": args.lanes, "nn": NN_DESC[args.nn], "sharding": f"pair-per-GPU, {world} GPU(s), no communication",
                            "l2": "each pair's clouds are uploaded from host memory inside the step (inputs > L2 in aggregate)"},
-                "roofline": None, "cpu_baseline": None,
+                "roofline": None, "cpu_baseline": cpu,
                 "e2e": {"value": evals / sec, "unit": "evals/s", "h2d_bytes_per_step": args.pairs * 2 * n * 24,
                         "d2h_bytes_per_step": args.pairs * (n * 24 + 13 * 8 + 12)},
-                "gpu_launches": int(iters) * 4 + args.pairs * 12, "clocks": clocks,
+                "gpu_launches": int(launches_all), "clocks": clocks,
                 "mean_iterations_per_pair": iters / args.pairs}
         print(json.dumps(line), flush=True)
     if dist:
@@ -423,10 +541,10 @@ def run_batch(args, rank, world, local_rank, torch, dist):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="horse", choices=list(WORKLOADS) + list(SYNTHETIC) + ["batch64k", "batch16k"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS) + list(SYNTHETIC) + ["batch64k", "batch16k"])
     ap.add_argument("--max-iter", type=int, default=None, help="override the workload's max_iter")
     ap.add_argument("--pairs", type=int, default=64, help="batch workloads: cloud pairs in total (dealt round-robin to the ranks)")
     ap.add_argument("--lanes", type=int, default=3, help="batch workloads: concurrent contexts per GPU")
@@ -434,9 +552,11 @@ def main():
                     help="brute: the exact brute-force search BASELINE.json's metric is quoted on (default); tree: the exact "
                          "bounding-box-hierarchy search (SURVEY 8f-4) - same results, `value` then counts brute-force-EQUIVALENT pairs")
     ap.add_argument("--skip-cpu-baseline", action="store_true", help="side runs only: leave cpu_baseline null (saves 10-30 s)")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="N > 1: weak = every rank holds a full copy of the scene as its shard (per-GPU work fixed); "
-                         "strong = the one scene is cut into N contiguous blocks")
+    ap.add_argument("--skip-parity", action="store_true", help="side runs only: N > 1 without the sharded-parity gate")
+    ap.add_argument("--no-secondary", action="store_true", help="side runs only: no secondary.horse block")
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="N > 1: strong (default) = the one scene is cut into N contiguous blocks; weak = every rank holds a full "
+                         "copy of the scene as its shard (per-GPU work fixed; a kernel-scaling probe)")
     args = ap.parse_args()
     if args.nn == "tree":
         os.environ["ICP_NN"] = "tree"        # read by icp_create (every context, batch lanes included)

@@ -54,13 +54,7 @@ def golden():
 
 
 def synthetic_pair(n, seed=0, angle_deg=5.0, noise=1e-3, shuffle=True, shift=(0.05, -0.03, 0.02)):
-    """Model ~ U[-1,1]^3; scene = R m + t + noise, optionally permuted."""
-    rng = np.random.default_rng(seed)
-    m = rng.uniform(-1.0, 1.0, (n, 3))
-    ax = np.array([1.0, 2.0, 3.0]) / np.sqrt(14.0)
-    a = np.deg2rad(angle_deg)
-    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
-    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
-    p = m @ R.T + np.asarray(shift, float) + noise * rng.standard_normal((n, 3))
-    perm = rng.permutation(n) if shuffle else np.arange(n)
-    return m, np.ascontiguousarray(p[perm]), perm
+    """Model ~ U[-1,1)^3; scene = R m + t + noise, optionally permuted: the SURVEY §8d recipe (splitmix64 / Box-Muller,
+    icp_b200/synth.py — the same generator bench.py uses) with seeds (1000, 2000, 3000) + seed."""
+    from icp_b200 import synth
+    return synth.pair(n, 1000 + seed, 2000 + seed, 3000 + seed, angle_deg=angle_deg, noise=noise, shift=shift, shuffle=shuffle)

@@ -53,7 +53,7 @@ def launches(tag, path):
     print("\n".join(out))
 
 
-def full(tag, rep, kernel):
+def full(tag, rep, kernel, workload=None):
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
@@ -76,6 +76,14 @@ def full(tag, rep, kernel):
     traffic = {"kernel": kernel, "source": f"profiles/{tag}_{kernel}_metrics.csv (ncu --set full, one launch)",
                "dram_bytes_read": to_bytes("dram__bytes_read.sum"), "dram_bytes_write": to_bytes("dram__bytes_write.sum")}
     traffic["dram_bytes_per_launch"] = traffic["dram_bytes_read"] + traffic["dram_bytes_write"]
+    path = os.path.join(PROF, f"{kernel}_traffic.json")
+    if workload:        # one capture per workload: bench.py prints roofline.traffic only for the workloads listed here
+        old = json.load(open(path)) if os.path.exists(path) else {}
+        wl = dict(old.get("workloads", {}))
+        wl[workload] = traffic["dram_bytes_per_launch"]
+        src = dict(old.get("sources", {}))
+        src[workload] = traffic["source"]
+        traffic = dict(old, workloads=wl, sources=src) if old else dict(traffic, workloads=wl, sources=src)
     json.dump(traffic, open(os.path.join(PROF, f"{kernel}_traffic.json"), "w"), indent=1)
     print(json.dumps(traffic))
 
@@ -86,9 +94,10 @@ if __name__ == "__main__":
     ap.add_argument("--launches")
     ap.add_argument("--rep")
     ap.add_argument("--kernel", default="nn_filter")
+    ap.add_argument("--workload", default=None, help="bench workload the capture was taken on (key of <kernel>_traffic.json's `workloads`)")
     a = ap.parse_args()
     os.makedirs(PROF, exist_ok=True)
     if a.launches:
         launches(a.tag, a.launches)
     if a.rep:
-        full(a.tag, a.rep, a.kernel)
+        full(a.tag, a.rep, a.kernel, a.workload)
