@@ -37,7 +37,10 @@ typedef enum icp_status {
     ICP_ERR_CUDA = -3,         /* a CUDA runtime call failed; see icp_last_error() */
     ICP_ERR_SIZE_MISMATCH = -4,/* np != nm   — reference: exit(-1), src/cpu.cc:44-47 */
     ICP_ERR_TOO_FEW = -5,      /* np < 4     — reference: exit(-1), src/cpu.cc:49-52 */
-    ICP_ERR_COMM = -6          /* NCCL unavailable or a collective failed */
+    ICP_ERR_COMM = -6          /* NCCL unavailable, a collective failed, or a peer did not arrive at an in-kernel exchange
+                                * within 20 s.  After the latter icp_run stops at once: new_p (icp_get_scene) holds the scene
+                                * as the last COMPLETED iteration left it, the transform is that iteration's, and the
+                                * communicator (mailbox sequence numbers) is no longer usable: destroy the contexts. */
 } icp_status;
 
 typedef struct icp_ctx icp_ctx;
@@ -71,8 +74,12 @@ const char* icp_last_error(void);
 const char* icp_version(void);
 
 /* ---- state: the ICP object (reference: CPU::ICP ctor src/cpu.hh:48-60, GPU::ICP src/GPU/gpu.hh:44-57)
- * icp_set_model  <- `m` (3 x nm).  Builds the FP64 SoA master and the FP32 shadow; uploaded once
- *                   (reference re-uploads every call: Matrix::toGpu, src/GPU/compute.cu:29-41).
+ * icp_set_model  <- `m` (3 x nm).  Builds the FP64 master (one 32-byte record per point) and the FP32 shadow;
+ *                   uploaded once (reference re-uploads every call: Matrix::toGpu, src/GPU/compute.cu:29-41).
+ *                   Non-finite input: NaN coordinates are handled as the reference's first-minimum scan handles them
+ *                   (a NaN model point is never chosen, unless it is point 0, which is then never left; a scene point
+ *                   with a NaN / infinite coordinate matches index 0).  A model with an INFINITE coordinate (no finite
+ *                   bounding box) is refused with ICP_ERR_INVALID.
  * icp_set_scene  <- `p` / `new_p` (3 x np).  Resets s = 1, R = I, t = 0 like the ctor.
  * icp_get_scene  -> `new_p` (src/cpu.hh:97).
  * icp_reset_scene   restores new_p to the cloud given to the last icp_set_scene without a host copy. */
@@ -129,8 +136,9 @@ int icp_get_stats(icp_ctx* ctx, icp_stats* out);
 /* Diagnostic (ICP_PROFILE=1 in the environment at icp_create): microseconds, relative to kernel entry, at which
  * block 0 of the last fused alignment kernel passed: 1 moments loop done, 2 block partials written, 3 grid
  * barrier passed, 4 partials reduced (+ peer exchange), 5 Horn solve done, 6 transform loop done, 7 exit of
- * the LAST block; slot 0 = microseconds between the end of the preceding nearest-neighbour kernel and entry. */
-int icp_get_trace(icp_ctx* ctx, double out_us[8]);
+ * the LAST block; slot 0 = microseconds between the end of the preceding nearest-neighbour kernel and entry (large
+ * models only: nn_exact stamps it); slots 8, 9 split step 4: partials re-read, block sum done. */
+int icp_get_trace(icp_ctx* ctx, double out_us[10]);
 
 /* ---- stateless one-shot forms (host pointers in, host results out) — back the reference-shaped
  * wrappers of src/GPU/gpu.hh:110-116.  Stateless for the caller; internally each host thread keeps one hidden

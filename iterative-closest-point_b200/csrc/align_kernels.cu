@@ -56,6 +56,10 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
 {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+#ifndef ICP_PEER_TIMEOUT_NS
+#define ICP_PEER_TIMEOUT_NS 20000000000ull
+#endif
+constexpr unsigned long long PEER_TIMEOUT_NS = ICP_PEER_TIMEOUT_NS;    // 20 s
 __device__ __forceinline__ unsigned long long globaltimer_ns()
 {
     unsigned long long t;
@@ -63,7 +67,10 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
     return t;
 }
 
-__device__ void peer_allreduce(const PeerComm& pc, const double* vals, int n, double* out, double* stage, int* ctl)
+// Returns false when a peer did not arrive within 20 s: CTL_COMM_TIMEOUT and CTL_DONE are set (every later kernel of
+// the loop returns at entry), nothing is consumed and the exchange number does not advance, so new_p stays as the
+// last COMPLETED iteration left it; the caller must not use `out`.
+__device__ bool peer_allreduce(const PeerComm& pc, const double* vals, int n, double* out, double* stage, int* ctl)
 {
     const int lane = threadIdx.x;                    // caller: threadIdx.x < 32
     // The exchange number lives in this rank's own mailbox and advances only when an exchange really happens, so
@@ -72,6 +79,7 @@ __device__ void peer_allreduce(const PeerComm& pc, const double* vals, int n, do
     const unsigned long long seq = ld_acquire_sys(&self->seq_local) + 1ull;
     __syncwarp();
     const int par = (int)(seq & 1ull);
+    bool arrived = true;
     if (lane < pc.world) {
         PeerMailbox* dst = pc.box[lane];             // post to rank `lane` (own mailbox included)
         for (int i = 0; i < n; ++i) dst->data[par][pc.rank][i] = vals[i];
@@ -81,11 +89,17 @@ __device__ void peer_allreduce(const PeerComm& pc, const double* vals, int n, do
         PeerMailbox* mine = pc.box[pc.rank];
         const unsigned long long t0 = globaltimer_ns();
         while (ld_acquire_sys(&mine->flag[par][lane]) != seq) {
-            if (globaltimer_ns() - t0 > 20000000000ull) { ctl[CTL_COMM_TIMEOUT] = 1; break; }   // 20 s: a peer died
+            if (globaltimer_ns() - t0 > PEER_TIMEOUT_NS) { arrived = false; break; }   // a peer died
         }
-        for (int i = 0; i < n; ++i) stage[lane * PEER_SLOT + i] = __ldcv(&mine->data[par][lane][i]);
+        if (arrived)
+            for (int i = 0; i < n; ++i) stage[lane * PEER_SLOT + i] = __ldcv(&mine->data[par][lane][i]);
     }
     __syncwarp();
+    if (__any_sync(0xffffffffu, !arrived)) {
+        if (lane == 0) { ctl[CTL_COMM_TIMEOUT] = 1; ctl[CTL_DONE] = 1; __threadfence(); }
+        __syncwarp();
+        return false;
+    }
     if (lane < n) {
         double acc = 0.0;
         for (int r = 0; r < pc.world; ++r) acc += stage[r * PEER_SLOT + lane];     // rank order: identical everywhere
@@ -93,20 +107,57 @@ __device__ void peer_allreduce(const PeerComm& pc, const double* vals, int n, do
     }
     if (lane == 0) { self->seq_local = seq; __threadfence(); }
     __syncwarp();
+    return true;
 }
 
 // ------------------------------------------------------------------------------------------------
 // K2: moments.
-// ICP_RED_MIN_CTAS (build-time variant, like ICP_NN_*): the kernel needs 126 registers because the Horn solve rides on
-// its last block, which leaves 2 CTAs per SM for the streaming loop; a bound of 4 trades spills in that tail (one
-// thread, once per launch) for twice the loads in flight on multi-million-point clouds.
-#ifdef ICP_RED_MIN_CTAS
-#define RED_BOUNDS __launch_bounds__(RED_THREADS, ICP_RED_MIN_CTAS)
-#else
-#define RED_BOUNDS __launch_bounds__(RED_THREADS)
-#endif
-__global__ void RED_BOUNDS
-moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
+// The streaming loop keeps TWO scene points in flight per thread (both index loads, then both gathers, then the sums) and
+// the kernel is bounded to 64 registers (4 CTAs per SM): on multi-million-point clouds the pass is HBM-latency bound and
+// needs ~6.5 MB in flight (round 1: one point per thread at 2 CTAs per SM = 37-40 % of the HBM copy peak on 2^22 points).
+// The Horn solve rides on the last block (one thread, once per launch); its spills under the register bound do not matter.
+__device__ __forceinline__ void moments_accumulate(double (&acc)[17], double ax, double ay, double az, double bx, double by,
+                                                   double bz)
+{
+    acc[0] += ax; acc[1] += ay; acc[2] += az;
+    acc[3] += bx; acc[4] += by; acc[5] += bz;
+    acc[6] += ax * bx; acc[7] += ax * by; acc[8] += ax * bz;
+    acc[9] += ay * bx; acc[10] += ay * by; acc[11] += ay * bz;
+    acc[12] += az * bx; acc[13] += az * by; acc[14] += az * bz;
+    acc[15] += ax * ax + ay * ay + az * az;
+    acc[16] += bx * bx + by * by + bz * bz;
+}
+
+__device__ __forceinline__ void moments_points(const Pt64* __restrict__ m64, const double* __restrict__ p64x,
+                                               const double* __restrict__ p64y, const double* __restrict__ p64z,
+                                               const int32_t* __restrict__ idx, int np, int nm, int n_blocks, double c0x,
+                                               double c0y, double c0z, double (&acc)[17], int* ctl)
+{
+    const int stride = n_blocks * RED_THREADS;
+    int j = blockIdx.x * RED_THREADS + threadIdx.x;
+    for (; j + stride < np; j += 2 * stride) {
+        int k0 = idx[j], k1 = idx[j + stride];
+        ICP_CHK_IDX(k0, nm, ctl);
+        ICP_CHK_IDX(k1, nm, ctl);
+        const double a0x = p64x[j], a0y = p64y[j], a0z = p64z[j];
+        const double a1x = p64x[j + stride], a1y = p64y[j + stride], a1z = p64z[j + stride];
+        double b0x, b0y, b0z, b1x, b1y, b1z;
+        ld_pt64(m64, k0, b0x, b0y, b0z);
+        ld_pt64(m64, k1, b1x, b1y, b1z);
+        moments_accumulate(acc, a0x - c0x, a0y - c0y, a0z - c0z, b0x - c0x, b0y - c0y, b0z - c0z);
+        moments_accumulate(acc, a1x - c0x, a1y - c0y, a1z - c0z, b1x - c0x, b1y - c0y, b1z - c0z);
+    }
+    if (j < np) {
+        int k = idx[j];
+        ICP_CHK_IDX(k, nm, ctl);
+        double bx, by, bz;
+        ld_pt64(m64, k, bx, by, bz);
+        moments_accumulate(acc, p64x[j] - c0x, p64y[j] - c0y, p64z[j] - c0z, bx - c0x, by - c0y, bz - c0z);
+    }
+}
+
+__global__ void __launch_bounds__(RED_THREADS, 4)
+moments_kernel(const Pt64* __restrict__ m64, int nm,
                const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
                const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
                double* __restrict__ mom, int* __restrict__ ctl, int honor_done, double* __restrict__ xf_fused,
@@ -121,18 +172,7 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
     double acc[17];
 #pragma unroll
     for (int i = 0; i < 17; ++i) acc[i] = 0.0;
-    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < np; j += gridDim.x * RED_THREADS) {
-        const int k = idx[j];
-        const double ax = p64x[j] - c0x, ay = p64y[j] - c0y, az = p64z[j] - c0z;
-        const double bx = m64x[k] - c0x, by = m64y[k] - c0y, bz = m64z[k] - c0z;
-        acc[0] += ax; acc[1] += ay; acc[2] += az;
-        acc[3] += bx; acc[4] += by; acc[5] += bz;
-        acc[6] += ax * bx; acc[7] += ax * by; acc[8] += ax * bz;
-        acc[9] += ay * bx; acc[10] += ay * by; acc[11] += ay * bz;
-        acc[12] += az * bx; acc[13] += az * by; acc[14] += az * bz;
-        acc[15] += ax * ax + ay * ay + az * az;
-        acc[16] += bx * bx + by * by + bz * bz;
-    }
+    moments_points(m64, p64x, p64y, p64z, idx, np, nm, (int)gridDim.x, c0x, c0y, c0z, acc, ctl);
     block_sum<17>(acc, red);
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -149,7 +189,7 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
         for (int i = 0; i < 17; ++i) tot[i] = 0.0;
         for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS)
 #pragma unroll
-            for (int i = 0; i < 17; ++i) tot[i] += partials[(size_t)b * 17 + i];
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)b * 17 + i]);
         block_sum<17>(tot, red);
         if (threadIdx.x == 0) {
             mom_s[0] = (double)np;
@@ -160,10 +200,13 @@ moments_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y,
         __syncthreads();
         if (threadIdx.x < 32) {
             // multi-GPU: the 18 sums of all ranks meet here, inside the kernel (peer mailboxes over NVLink)
-            if (pc.world > 0) peer_allreduce(pc, mom_s, MOM_N, mom_s, stage, ctl);
-            if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
-            __syncwarp();
-            if (threadIdx.x == 0 && xf_fused) horn_solve(geo, mom_s, xf_fused);   // K3 rides on K2's last block
+            bool ok = true;
+            if (pc.world > 0) ok = peer_allreduce(pc, mom_s, MOM_N, mom_s, stage, ctl);
+            if (ok) {
+                if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
+                __syncwarp();
+                if (threadIdx.x == 0 && xf_fused) horn_solve(geo, mom_s, xf_fused);   // K3 rides on K2's last block
+            }
         }
     }
 }
@@ -347,47 +390,80 @@ __global__ void solve_kernel(const double* __restrict__ geo, const double* __res
     if (threadIdx.x == 0) horn_solve(geo, mom, xf);
 }
 
-// The per-point body of K4, shared by transform_kernel and align_fused_kernel.  Warps stay converged over
-// the last (ragged) 32 points so that the warp holding point np-1 can refresh the FP32 shadow's padding
-// [np, np_pad) cooperatively (one thread doing it alone costs ~20 us on horse: 667 dependent stores).
-__device__ __forceinline__ void transform_points(const double* __restrict__ m64x, const double* __restrict__ m64y,
-                                                 const double* __restrict__ m64z, double* __restrict__ p64x,
+// The per-point body of K4, shared by transform_kernel and align_fused_kernel.  Two scene points are in flight per
+// thread (j and j + stride: both index loads, both gathers, then the arithmetic; the per-thread summation order is the
+// same as with one point per trip).  Warps stay converged over the last (ragged) 32 points so that the warp holding
+// point np-1 can refresh the FP32 shadow's padding [np, np_pad) cooperatively (one thread doing it alone costs ~20 us
+// on horse: 667 dependent stores).
+struct XfPoint {
+    double x, y, z, mx, my, mz;
+    int j;
+    bool act;
+};
+
+__device__ __forceinline__ XfPoint xf_load(const Pt64* __restrict__ m64, int nm, const double* __restrict__ p64x,
+                                           const double* __restrict__ p64y, const double* __restrict__ p64z,
+                                           const int32_t* __restrict__ idx, int np, int j0, int* ctl)
+{
+    XfPoint q;
+    q.act = j0 < np;
+    q.j = q.act ? j0 : np - 1;         // inactive lanes of the last warp re-read point np-1, which lives in this same warp
+    int k = idx[q.j];
+    ICP_CHK_IDX(k, nm, ctl);
+    q.x = p64x[q.j]; q.y = p64y[q.j]; q.z = p64z[q.j];
+    ld_pt64(m64, k, q.mx, q.my, q.mz);
+    return q;
+}
+
+__device__ __forceinline__ void xf_apply(const XfPoint& q, int j0, double* __restrict__ p64x, double* __restrict__ p64y,
+                                         double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy,
+                                         float* __restrict__ phz, int np, int np_pad, const double (&sr)[9], double tx,
+                                         double ty, double tz, double c0x, double c0y, double c0z, int in_place, double& acc)
+{
+    const double x = q.x, y = q.y, z = q.z;
+    const double qx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
+    const double qy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
+    const double qz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
+    const double ex = __dsub_rn(q.mx, qx), ey = __dsub_rn(q.my, qy), ez = __dsub_rn(q.mz, qz);
+    if (q.act) acc += __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
+    if (in_place) {                                   // uniform
+        float fx = (float)(qx - c0x), fy = (float)(qy - c0y), fz = (float)(qz - c0z);
+        if (q.act) {
+            p64x[q.j] = qx; p64y[q.j] = qy; p64z[q.j] = qz;
+            phx[q.j] = fx; phy[q.j] = fy; phz[q.j] = fz;
+        }
+        const unsigned has_last = __ballot_sync(0xffffffffu, j0 == np - 1);
+        if (has_last) {                               // warp-uniform: refresh the padding = last real point
+            const int src = __ffs(has_last) - 1;
+            fx = __shfl_sync(0xffffffffu, fx, src);
+            fy = __shfl_sync(0xffffffffu, fy, src);
+            fz = __shfl_sync(0xffffffffu, fz, src);
+            for (int q2 = np + (int)(threadIdx.x & 31); q2 < np_pad; q2 += 32) { phx[q2] = fx; phy[q2] = fy; phz[q2] = fz; }
+        }
+    }
+}
+
+__device__ __forceinline__ void transform_points(const Pt64* __restrict__ m64, int nm, double* __restrict__ p64x,
                                                  double* __restrict__ p64y, double* __restrict__ p64z,
                                                  float* __restrict__ phx, float* __restrict__ phy,
                                                  float* __restrict__ phz, const int32_t* __restrict__ idx, int np,
                                                  int np_pad, const double (&sr)[9], double tx, double ty, double tz,
                                                  double c0x, double c0y, double c0z, int in_place, int n_blocks,
-                                                 double& acc)
+                                                 double& acc, int* ctl)
 {
     const int np_round = (np + 31) & ~31;
-    for (int j0 = blockIdx.x * RED_THREADS + threadIdx.x; j0 < np_round; j0 += n_blocks * RED_THREADS) {
-        const bool act = j0 < np;
-        const int j = act ? j0 : np - 1;
-        const int k = idx[j];
-        const double x = p64x[j], y = p64y[j], z = p64z[j];
-        const double qx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
-        const double qy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
-        const double qz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
-        const double ex = __dsub_rn(m64x[k], qx), ey = __dsub_rn(m64y[k], qy), ez = __dsub_rn(m64z[k], qz);
-        if (act) acc += __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
-        if (in_place) {                                   // uniform
-            // every lane has READ its point before any lane of this warp writes (the inactive lanes of the
-            // last warp re-read point np-1, which lives in this same warp)
-            __syncwarp();
-            float fx = (float)(qx - c0x), fy = (float)(qy - c0y), fz = (float)(qz - c0z);
-            if (act) {
-                p64x[j] = qx; p64y[j] = qy; p64z[j] = qz;
-                phx[j] = fx; phy[j] = fy; phz[j] = fz;
-            }
-            const unsigned has_last = __ballot_sync(0xffffffffu, j0 == np - 1);
-            if (has_last) {                               // warp-uniform: refresh the padding = last real point
-                const int src = __ffs(has_last) - 1;
-                fx = __shfl_sync(0xffffffffu, fx, src);
-                fy = __shfl_sync(0xffffffffu, fy, src);
-                fz = __shfl_sync(0xffffffffu, fz, src);
-                for (int q = np + (int)(threadIdx.x & 31); q < np_pad; q += 32) { phx[q] = fx; phy[q] = fy; phz[q] = fz; }
-            }
-        }
+    const int stride = n_blocks * RED_THREADS;
+    for (int jA = blockIdx.x * RED_THREADS + threadIdx.x; jA < np_round; jA += 2 * stride) {
+        const int jB = jA + stride;
+        const bool hasB = jB < np_round;              // warp-uniform (32 consecutive, 32-aligned indices per warp)
+        const XfPoint A = xf_load(m64, nm, p64x, p64y, p64z, idx, np, jA, ctl);
+        XfPoint B = A;
+        if (hasB) B = xf_load(m64, nm, p64x, p64y, p64z, idx, np, jB, ctl);
+        // every lane has READ its points before any lane of this warp writes (only the warp that holds point np-1 has
+        // inactive lanes, and they re-read that very point)
+        __syncwarp();
+        xf_apply(A, jA, p64x, p64y, p64z, phx, phy, phz, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z, in_place, acc);
+        if (hasB) xf_apply(B, jB, p64x, p64y, p64z, phx, phy, phz, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z, in_place, acc);
     }
 }
 
@@ -399,7 +475,7 @@ __device__ __forceinline__ void transform_points(const double* __restrict__ m64x
 // finish = 1: the last block also closes the ICP iteration (src/cpu.cc:67-77): the reference adds the
 // two residual sums, which are the same expression evaluated twice, so err = 2*sum/np.
 __global__ void __launch_bounds__(RED_THREADS)
-transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
+transform_kernel(const Pt64* __restrict__ m64, int nm,
                  const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
                  double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
                  const int32_t* __restrict__ idx, int np, int np_pad, const double* __restrict__ xf, int in_place,
@@ -418,8 +494,8 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
     const double tx = xf[10], ty = xf[11], tz = xf[12];
     const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
     double acc[1] = {0.0};
-    transform_points(m64x, m64y, m64z, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
-                     in_place, (int)gridDim.x, acc[0]);
+    transform_points(m64, nm, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
+                     in_place, (int)gridDim.x, acc[0], ctl);
     block_sum<1>(acc, red);
     if (threadIdx.x == 0) {
         partials[blockIdx.x] = acc[0];
@@ -436,8 +512,10 @@ transform_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         if (threadIdx.x == 0) tot_s[0] = tot[0];
         __syncthreads();
         if (threadIdx.x < 32) {
-            if (pc.world > 0) peer_allreduce(pc, tot_s, 1, tot_s, stage, ctl);
-            if (threadIdx.x == 0) {
+            bool ok = true;
+            if (pc.world > 0) ok = peer_allreduce(pc, tot_s, 1, tot_s, stage, ctl);
+            if (threadIdx.x == 0 && !ok) ctl[CTL_TICKET_ERR] = 0;
+            if (threadIdx.x == 0 && ok) {
                 const double total = tot_s[0];
                 err_sum[0] = total;
                 ctl[CTL_TICKET_ERR] = 0;
@@ -476,7 +554,7 @@ __global__ void finish_kernel(const double* __restrict__ err_sum, double n_globa
 //   phase T  q = sR p + t, residual; in_place writes new_p and its FP32 shadow  -> partials_err[block]
 //   last block (ticket): total residual (+ peer exchange), closes the iteration when `finish`.
 __global__ void __launch_bounds__(RED_THREADS, 2)
-align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
+align_fused_kernel(const Pt64* __restrict__ m64, int nm,
                    const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
                    double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
                    const int32_t* __restrict__ idx, int np, int np_pad, double* __restrict__ partials,
@@ -502,18 +580,7 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
     double acc[17];
 #pragma unroll
     for (int i = 0; i < 17; ++i) acc[i] = 0.0;
-    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < np; j += nb * RED_THREADS) {
-        const int k = idx[j];
-        const double ax = p64x[j] - c0x, ay = p64y[j] - c0y, az = p64z[j] - c0z;
-        const double bx = m64x[k] - c0x, by = m64y[k] - c0y, bz = m64z[k] - c0z;
-        acc[0] += ax; acc[1] += ay; acc[2] += az;
-        acc[3] += bx; acc[4] += by; acc[5] += bz;
-        acc[6] += ax * bx; acc[7] += ax * by; acc[8] += ax * bz;
-        acc[9] += ay * bx; acc[10] += ay * by; acc[11] += ay * bz;
-        acc[12] += az * bx; acc[13] += az * by; acc[14] += az * bz;
-        acc[15] += ax * ax + ay * ay + az * az;
-        acc[16] += bx * bx + by * by + bz * bz;
-    }
+    moments_points(m64, p64x, p64y, p64z, idx, np, nm, nb, c0x, c0y, c0z, acc, ctl);
     TRACE(1);
     block_sum<17>(acc, red);
     if (threadIdx.x == 0)
@@ -531,7 +598,9 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
         for (int b = threadIdx.x; b < nb; b += RED_THREADS)
 #pragma unroll
             for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)i * nb + b]);
+        TRACE(10);
         block_sum<17>(tot, red);
+        TRACE(11);
         if (threadIdx.x == 0) {
             mom_s[0] = (double)np;
 #pragma unroll
@@ -542,12 +611,13 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
     if (pc.world > 0) {
         if (blockIdx.x == 0) {
             if (threadIdx.x < 32) {
-                peer_allreduce(pc, mom_s, MOM_N, mom_s, stage, ctl);
-                if (threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
+                const bool ok = peer_allreduce(pc, mom_s, MOM_N, mom_s, stage, ctl);
+                if (ok && threadIdx.x < MOM_N) mom[threadIdx.x] = mom_s[threadIdx.x];
                 __threadfence();
             }
         }
         grid.sync();
+        if (*(volatile int*)&ctl[CTL_COMM_TIMEOUT]) return;      // a peer died: uniform over the grid, new_p untouched
         if (blockIdx.x != 0 && threadIdx.x < MOM_N) mom_s[threadIdx.x] = __ldcg(&mom[threadIdx.x]);
         __syncthreads();
     }
@@ -570,8 +640,8 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
     for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(s, xf_s[1 + i]);
     const double tx = xf_s[10], ty = xf_s[11], tz = xf_s[12];
     double e[1] = {0.0};
-    transform_points(m64x, m64y, m64z, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
-                     in_place, nb, e[0]);
+    transform_points(m64, nm, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
+                     in_place, nb, e[0], ctl);
     TRACE(6);
     block_sum<1>(e, red);
     if (threadIdx.x == 0) {
@@ -589,8 +659,10 @@ align_fused_kernel(const double* __restrict__ m64x, const double* __restrict__ m
         if (threadIdx.x == 0) mom_s[0] = tot[0];
         __syncthreads();
         if (threadIdx.x < 32) {
-            if (pc.world > 0) peer_allreduce(pc, mom_s, 1, mom_s, stage, ctl);
-            if (threadIdx.x == 0) {
+            bool ok = true;
+            if (pc.world > 0) ok = peer_allreduce(pc, mom_s, 1, mom_s, stage, ctl);
+            if (threadIdx.x == 0 && !ok) ctl[CTL_TICKET_ERR] = 0;
+            if (threadIdx.x == 0 && ok) {
                 const double total = mom_s[0];
                 err_sum[0] = total;
                 ctl[CTL_TICKET_ERR] = 0;
@@ -697,16 +769,16 @@ __global__ void model_geo_kernel(double* geo)
 
 // AoS FP64 model -> FP64 SoA master + FP32 float4 shadow (c0-relative), sentinel padding.
 __global__ void model_build_kernel(const double* __restrict__ xyz, int64_t nm, int64_t nm_pad,
-                                   const double* __restrict__ geo, double* __restrict__ m64x,
-                                   double* __restrict__ m64y, double* __restrict__ m64z, float4* __restrict__ mhat)
+                                   const double* __restrict__ geo, Pt64* __restrict__ m64, float4* __restrict__ mhat)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nm_pad) return;
     if (i < nm) {
         const double x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
-        m64x[i] = x; m64y[i] = y; m64z[i] = z;
+        m64[i] = Pt64{x, y, z, 0.0};
         mhat[i] = make_float4((float)(x - geo[0]), (float)(y - geo[1]), (float)(z - geo[2]), 0.f);
     } else {
+        m64[i] = Pt64{0.0, 0.0, 0.0, 0.0};
         mhat[i] = make_float4(NN_SENTINEL, NN_SENTINEL, NN_SENTINEL, 0.f);
     }
 }
@@ -782,8 +854,7 @@ __global__ void scene_export_kernel(int64_t np, const int32_t* __restrict__ perm
 }
 
 __global__ void indices_export_kernel(int64_t np, const int32_t* __restrict__ perm, const int32_t* __restrict__ idx,
-                                      const double* __restrict__ m64x, const double* __restrict__ m64y,
-                                      const double* __restrict__ m64z, int32_t* __restrict__ idx_out,
+                                      const Pt64* __restrict__ m64, int nm, int32_t* __restrict__ idx_out,
                                       double* __restrict__ Y_out)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -791,7 +862,11 @@ __global__ void indices_export_kernel(int64_t np, const int32_t* __restrict__ pe
     const int64_t d = perm[i];
     const int k = idx[i];
     if (idx_out) idx_out[d] = k;
-    if (Y_out) { Y_out[3 * d] = m64x[k]; Y_out[3 * d + 1] = m64y[k]; Y_out[3 * d + 2] = m64z[k]; }
+    if (Y_out && (unsigned)k < (unsigned)nm) {
+        double mx, my, mz;
+        ld_pt64(m64, k, mx, my, mz);
+        Y_out[3 * d] = mx; Y_out[3 * d + 1] = my; Y_out[3 * d + 2] = mz;
+    }
 }
 
 // mu_p, mu_y from the moments (src/cpu.cc:113-114)
@@ -834,7 +909,7 @@ void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int 
 {
     PeerComm pc;
     if (peer) pc = *peer;
-    moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
+    moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64, (int)m.nm, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
                                                      (int)s.np, partials, mom, ctl, honor_done, xf_fused, pc);
 }
 
@@ -849,7 +924,7 @@ void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, in
 {
     PeerComm pc;
     if (peer) pc = *peer;
-    transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
+    transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64, (int)m.nm, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
                                                        s.phy, s.phz, s.idx, (int)s.np, (int)s.np_pad, xf, in_place,
                                                        partials, err_sum, ctl, honor_done, finish, n_global,
                                                        threshold, err_hist, pc);
@@ -872,11 +947,13 @@ int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, i
     PeerComm pc;
     if (peer) pc = *peer;
     int np = (int)s.np, np_pad = (int)s.np_pad;
-    const double *a0 = m.m64x, *a1 = m.m64y, *a2 = m.m64z, *a3 = m.geo;
+    const Pt64* a0 = m.m64;
+    int nm = (int)m.nm;
+    const double* a3 = m.geo;
     double *b0 = s.p64x, *b1 = s.p64y, *b2 = s.p64z;
     float *f0 = s.phx, *f1 = s.phy, *f2 = s.phz;
     const int32_t* ix = s.idx;
-    void* args[] = {&a0, &a1, &a2, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum,
+    void* args[] = {&a0, &nm, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum,
                     &ctl, &honor_done, &in_place, &finish, &n_global, &threshold, &err_hist, &pc, &trace};
     return (int)cudaLaunchCooperativeKernel((const void*)align_fused_kernel, dim3(n_blocks), dim3(RED_THREADS), args, 0, st);
 }
@@ -900,8 +977,7 @@ void launch_model_geo(double* geo, cudaStream_t st) { model_geo_kernel<<<1, 1, 0
 
 void launch_model_build(const double* xyz_aos, const ModelDev& m, cudaStream_t st)
 {
-    model_build_kernel<<<grid1d(m.nm_pad, 256), 256, 0, st>>>(xyz_aos, m.nm, m.nm_pad, m.geo, m.m64x, m.m64y, m.m64z,
-                                                              m.mhat);
+    model_build_kernel<<<grid1d(m.nm_pad, 256), 256, 0, st>>>(xyz_aos, m.nm, m.nm_pad, m.geo, m.m64, m.mhat);
 }
 
 void launch_scene_keys(const double* xyz_aos, int64_t n, const double* bbox, uint32_t* keys, int32_t* vals,
@@ -929,8 +1005,7 @@ void launch_scene_export(const SceneDev& s, double* xyz_aos_out, cudaStream_t st
 
 void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_out, double* Y_aos_out, cudaStream_t st)
 {
-    indices_export_kernel<<<grid1d(s.np, 256), 256, 0, st>>>(s.np, s.perm, s.idx, m.m64x, m.m64y, m.m64z, idx_out,
-                                                             Y_aos_out);
+    indices_export_kernel<<<grid1d(s.np, 256), 256, 0, st>>>(s.np, s.perm, s.idx, m.m64, (int)m.nm, idx_out, Y_aos_out);
 }
 
 void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st)

@@ -110,8 +110,7 @@ struct icp_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
-    int forced_ctas = 0;
-    int min_units = 0;                     // ICP_NN_MIN_UNITS: least chunk-units per filter CTA (0 = one staged tile = 8)
+    bool model0_nan = false;               // model point 0 has a NaN coordinate: the reference's first-minimum scan never leaves it
     size_t cap_nm = 0, cap_np = 0;         // allocated capacities (points): buffers only ever grow
     // fused alignment kernel (cooperative) and the peer-memory exchange it carries when world > 1
     int align_blocks_max = 148;
@@ -127,16 +126,6 @@ struct icp_ctx {
     int* progress_arg = nullptr;           // what nn_pass hands to the filter kernel (set by icp_run only)
     int lookahead = 3;                     // ICP_LOOKAHEAD: iterations icp_run keeps enqueued ahead of the device (0 = all at once)
     bool profile = false;                  // ICP_PROFILE=1: events between all kernels of icp_run (adds ~us per iteration)
-    // ICP_GRAPH=1 (experiment, off by default): iterations >= 1 of icp_run are ONE instantiated CUDA graph (the
-    // iteration's kernels as captured from the plain enqueue path), re-launched per iteration under the same
-    // look-ahead rule.  The graph is kept while every captured kernel argument stays the same (GraphKey).
-    int graph_mode = 0;
-    cudaGraph_t loop_graph_tmpl = nullptr; // kept: its event-record node handles address the nodes of loop_graph
-    cudaGraphExec_t loop_graph = nullptr;
-    cudaGraphNode_t graph_ev_node[2] = {nullptr, nullptr};   // event records before / after the filter kernel
-    bool capturing = false;                // nn_pass records its events as external event nodes
-    int graph_kernels = 0;                 // kernels inside loop_graph
-    struct GraphKey { const void* p[24]; long long n[12]; double d[2]; } graph_key{};
 };
 
 namespace {
@@ -220,11 +209,14 @@ int ensure_tree(icp_ctx* c)
 }
 
 // Stream-K decomposition of the filter (see nn_filter_kernel): the grid is a whole number of waves of
-// 4 CTAs per SM, each CTA owning an equal contiguous range of chunk-units.  One wave while a CTA's range stays
-// below ~1024 chunks (horse: 61.6 chunks per CTA); beyond that, more waves of ~1024-chunk ranges, so that the
+// NN_MIN_CTAS CTAs per SM, each CTA owning an equal contiguous range of chunk-units.  One wave while a CTA's range
+// stays below ~64 K model points x one scene tile; beyond that, more waves of such ranges, so that the
 // hardware's dynamic block scheduling evens out SM-to-SM speed differences on long runs (measured on 2^20
-// points: a single wave of 28 000-chunk ranges is 1.9 % slower than 28 waves).  Never so many CTAs that one
-// gets less than a staged model tile (8 chunks).  n_splits = the most partial results a scene tile can receive.
+// points: a single wave of 28 000-chunk ranges is 1.9 % slower than 28 waves).
+// Small clouds: a CTA normally gets at least one staged model tile (NN_TM / NN_G chunks), but never so few CTAs that
+// SMs stay empty while there are units to hand out (round 2, profiles/r02a_minunits.md: cow's filter 35 -> 25 us with one
+// unit per CTA; with more units than SMs the staged-tile floor wins again).
+// n_splits = the most partial results a scene tile can receive.
 void choose_splits(icp_ctx* c)
 {
     const long long n_tiles = c->s.np_pad / NN_TILE;
@@ -235,11 +227,10 @@ void choose_splits(icp_ctx* c)
     long long waves = (total + per_cta * wave - 1) / (per_cta * wave);
     if (waves < 1) waves = 1;
     long long n_cta = wave * waves;
-    if (c->forced_ctas > 0) n_cta = c->forced_ctas;
-    // ICP_NN_MIN_UNITS (experiment): fewer chunks per CTA than one staged tile spreads a SMALL cloud over more SMs (cow:
-    // 144 chunk-units = 18 CTAs of 8 on a 148-SM GPU); the kernel then stages a whole tile for the chunks it needs.
-    const long long min_units = c->min_units > 0 ? c->min_units : NN_TM / NN_G;
-    if (n_cta > total / min_units) n_cta = total / min_units;
+    long long cap = total / (NN_TM / NN_G);             // one staged tile per CTA ...
+    const long long one_per_sm = total < c->sm_count ? total : c->sm_count;
+    if (cap < one_per_sm) cap = one_per_sm;             // ... unless that leaves SMs without work
+    if (n_cta > cap) n_cta = cap;
     if (n_cta < 1) n_cta = 1;
     c->sc.n_cta = (int)n_cta;
     c->sc.n_splits = (int)((n_cta + n_tiles - 1) / n_tiles + 1);
@@ -270,18 +261,16 @@ int allreduce(icp_ctx* c, double* buf, size_t n)
     return ICP_OK;
 }
 
+// Models up to this size are rescanned for undecided points inside nn_refine (no nn_exact launch); larger ones queue
+// them for nn_exact, which shares one scan of the model between four queued points of any block.
+constexpr int64_t INLINE_EXACT_MAX_NM = 131072;
+
 // One closest-matrix pass (K1) on the stream.  use_prev: idx[] holds valid matches of the same model (tree mode
 // starts every search from them).
 void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent_t e1, cudaEvent_t e2 = nullptr,
              cudaEvent_t e3 = nullptr)
 {
-    // inside a stream capture (ICP_GRAPH) a plain cudaEventRecord is only a dependency marker; the external form
-    // becomes an event-record node that really records on every launch of the graph
-    auto record = [c](cudaEvent_t e) {
-        if (c->capturing) cudaEventRecordWithFlags(e, c->st, cudaEventRecordExternal);
-        else cudaEventRecord(e, c->st);
-    };
-    if (e0) record(e0);
+    if (e0) cudaEventRecord(e0, c->st);
     if (tree_active(c) && c->tree_built[tree_use_wide(c)]) {
         // measured (profiles/r01h_tree.md): a warp per point wins while the grid is a few waves (cow 0.014 vs 0.052 ms,
         // horse 128 vs 285 us per search: the slowest thread no longer sets the kernel time); a thread per point
@@ -290,19 +279,24 @@ void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent
             launch_nn_wtree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
         else
             launch_nn_tree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
-        if (e1) cudaEventRecord(e1, c->st);
-        if (e2) cudaEventRecord(e2, c->st);
-        if (e3) cudaEventRecord(e3, c->st);
         c->stats.kernels_launched += 1;
-        return;
+    } else {
+        const int inline_exact = c->m.nm <= INLINE_EXACT_MAX_NM;
+        launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st, c->progress_arg);
+        if (e1) cudaEventRecord(e1, c->st);
+        launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, inline_exact, c->st);
+        if (e2) cudaEventRecord(e2, c->st);
+        e1 = e2 = nullptr;
+        if (!inline_exact)
+            launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st, c->profile ? c->d_trace : nullptr);
+        c->stats.kernels_launched += inline_exact ? 2 : 3;
     }
-    launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st, c->progress_arg);
-    if (e1) record(e1);
-    launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st);
+    // Model point 0 is NaN: d(0) is NaN for every scene point and minCoeff's strict `<` never replaces it
+    // (src/cpu.cc:21-22), so the reference matches everything to index 0; the kernels above ignore NaN candidates.
+    if (c->model0_nan) cudaMemsetAsync(c->s.idx, 0, (size_t)c->s.np * sizeof(int32_t), c->st);
+    if (e1) cudaEventRecord(e1, c->st);
     if (e2) cudaEventRecord(e2, c->st);
-    launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st, c->profile ? c->d_trace : nullptr);
     if (e3) cudaEventRecord(e3, c->st);
-    c->stats.kernels_launched += 3;
 }
 
 // Alignment step (K2 -> K3 -> K4) of one iteration.  Two device-only forms, both able to carry the multi-GPU
@@ -356,7 +350,8 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
     // auto: the cooperative kernel where it was measured faster (one GPU, nothing else on it: 11.17 vs 11.27 ms per
     // horse loop), the split pair with peers (its second grid barrier costs more than a launch: 11.65 vs 11.61 ms
     // at N = 2) and in batch lanes (no co-residency requirement between concurrent contexts).
-    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->is_lane);
+    // Large scenes take the split pair as well: no co-residency limit on the grid (2^22 points: 225 vs 245 us).
+    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->is_lane && c->s.np <= 262144);
     if (fused) {
         const int e = launch_align_fused(c->m, c->s, c->d_partials, fused_blocks(c), c->d_mom, c->d_xf, c->d_err_sum,
                                          c->d_ctl, honor_done, in_place, finish, n_global, threshold, c->d_err_hist, peers,
@@ -370,81 +365,6 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
         launched = 2;
     }
     return launched;
-}
-
-// ICP_GRAPH: everything a captured iteration depends on.  Buffers of one group are (re)allocated together, so
-// the pointers below change whenever any kernel argument does; sizes, grid shapes and modes are listed explicitly.
-void fill_graph_key(const icp_ctx* c, double n_global, double threshold, icp_ctx::GraphKey& k)
-{
-    memset(&k, 0, sizeof(k));
-    const void* p[] = {c->m.m64x, c->m.m64y, c->m.m64z, c->m.mhat, c->m.geo, c->s.p64x, c->s.p64y, c->s.p64z, c->s.phx,
-                       c->s.phy, c->s.phz, c->s.idx, c->sc.best, c->sc.runner, c->sc.chunk, c->sc.amb_list, c->sc.amb_thr,
-                       c->sc.seg_v, c->sc.seg_k, c->sc.batch_ticket, c->d_err_hist, c->d_partials, c->progress_arg,
-                       c->peer_ready ? (const void*)c->peer.box[0] : nullptr};
-    static_assert(sizeof(p) == sizeof(k.p), "GraphKey::p");
-    memcpy(k.p, p, sizeof(p));
-    const long long n[] = {c->m.nm, c->m.nm_pad, c->s.np, c->s.np_pad, c->sc.n_cta, c->sc.n_splits, (long long)c->sc.seg_cap,
-                           c->n_red_blocks, c->align_mode, (c->comm ? 1 : 0) | (c->peer_ready ? 2 : 0) | (c->is_lane ? 4 : 0),
-                           c->peer.world * 64 + c->peer.rank, fused_blocks(c)};
-    static_assert(sizeof(n) == sizeof(k.n), "GraphKey::n");
-    memcpy(k.n, n, sizeof(n));
-    k.d[0] = n_global;
-    k.d[1] = threshold;
-}
-
-// Captures one iteration (K1 filter/refine/exact + the alignment step, exactly as the plain path enqueues them) into
-// c->loop_graph.  Any failure leaves the stream usable, clears the error and switches graph mode off for this context.
-bool capture_iteration(icp_ctx* c, double n_global, double threshold)
-{
-    auto drop = [c]() {
-        if (c->loop_graph) { cudaGraphExecDestroy(c->loop_graph); c->loop_graph = nullptr; }
-        if (c->loop_graph_tmpl) { cudaGraphDestroy(c->loop_graph_tmpl); c->loop_graph_tmpl = nullptr; }
-        c->graph_ev_node[0] = c->graph_ev_node[1] = nullptr;
-    };
-    drop();
-    const int launched_before = c->stats.kernels_launched;
-    cudaGraph_t g = nullptr;
-    // placeholders for the two filter events: iteration 1's own pair (icp_run re-targets the nodes before every launch)
-    cudaEvent_t ea = c->ev_filter[2], eb = c->ev_filter[3];
-    bool ok = cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
-    if (ok) {
-        c->capturing = true;
-        nn_pass(c, 1, 1, ea, eb);
-        c->capturing = false;
-        const int launched = align_step(c, 1, 1, 1, n_global, threshold);
-        ok = launched > 0;
-        if (ok) c->stats.kernels_launched += launched;
-        const cudaError_t e = cudaStreamEndCapture(c->st, &g);      // always: the stream must leave capture mode
-        ok = ok && e == cudaSuccess && g != nullptr;
-    }
-    c->graph_kernels = c->stats.kernels_launched - launched_before;
-    c->stats.kernels_launched = launched_before;
-    if (ok) {                                                       // find the two event-record nodes
-        size_t n = 0;
-        ok = cudaGraphGetNodes(g, nullptr, &n) == cudaSuccess && n > 0 && n < 64;
-        cudaGraphNode_t nodes[64];
-        if (ok) ok = cudaGraphGetNodes(g, nodes, &n) == cudaSuccess;
-        for (size_t i = 0; ok && i < n; ++i) {
-            cudaGraphNodeType t;
-            cudaEvent_t ev = nullptr;
-            if (cudaGraphNodeGetType(nodes[i], &t) != cudaSuccess) { ok = false; break; }
-            if (t != cudaGraphNodeTypeEventRecord) continue;
-            if (cudaGraphEventRecordNodeGetEvent(nodes[i], &ev) != cudaSuccess) { ok = false; break; }
-            if (ev == ea) c->graph_ev_node[0] = nodes[i];
-            if (ev == eb) c->graph_ev_node[1] = nodes[i];
-        }
-        ok = ok && c->graph_ev_node[0] && c->graph_ev_node[1];
-    }
-    if (ok) ok = cudaGraphInstantiate(&c->loop_graph, g, 0) == cudaSuccess;
-    c->loop_graph_tmpl = g;
-    if (!ok) {
-        cudaGetLastError();
-        drop();
-        c->graph_mode = 0;
-        return false;
-    }
-    fill_graph_key(c, n_global, threshold, c->graph_key);
-    return true;
 }
 
 int reset_ctl(icp_ctx* c)
@@ -468,7 +388,8 @@ int pull_amb_stats(icp_ctx* c)
     CK(cudaMemcpyAsync(ctl, c->d_ctl, sizeof(ctl), cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
     c->stats.rerank_full += ctl[CTL_AMB_TOTAL];
-    c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
+    c->stats.rerank_chunk += c->s.np - ctl[CTL_AMB_TOTAL];
+    if (ctl[CTL_BOUNDS]) { g_err = "bounds check failed at csrc line " + std::to_string(ctl[CTL_BOUNDS]); return ICP_ERR_CUDA; }
     return ICP_OK;
 }
 
@@ -480,18 +401,9 @@ extern "C" {
 const char* icp_last_error(void) { return g_err.c_str(); }
 const char* icp_version(void) { return "icp_b200 0.1 (sm_100a)"; }
 
-int icp_create(icp_ctx** out, int device)
+static int create_body(icp_ctx* c, int device)
 {
-    if (!out) return ICP_ERR_INVALID;
-    *out = nullptr;
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
-        g_err = "no usable CUDA device (this library has no CPU fallback)";
-        cudaGetLastError();
-        return ICP_ERR_NO_DEVICE;
-    }
     CK(cudaSetDevice(device));
-    icp_ctx* c = new icp_ctx();
     c->device = device;
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, device));
@@ -502,26 +414,41 @@ int icp_create(icp_ctx** out, int device)
     int r;
     if ((r = dalloc(&c->d_mom, MOM_N)) || (r = dalloc(&c->d_xf, XF_N)) || (r = dalloc(&c->d_err_sum, 1)) ||
         (r = dalloc(&c->d_out6, 8)) || (r = dalloc(&c->d_ctl, CTL_N)) || (r = dalloc(&c->m.geo, 16)) ||
-        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 18))) {
-        icp_destroy(c);                       // frees whatever was allocated so far
+        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 18)) || (r = dalloc(&c->d_trace, 16)))
         return r;
-    }
-    if ((r = dalloc(&c->d_trace, 16))) { icp_destroy(c); return r; }
     CK(cudaMemset(c->d_trace, 0, 16 * sizeof(unsigned long long)));
     c->align_blocks_max = align_fused_max_blocks(c->sm_count);
     if (const char* e = getenv("ICP_COMM")) c->force_nccl = !strcmp(e, "nccl");
     if (const char* e = getenv("ICP_ALIGN")) c->align_mode = !strcmp(e, "fused") ? 1 : (!strcmp(e, "split") ? 2 : 0);
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
-    if (const char* e = getenv("ICP_GRAPH")) c->graph_mode = atoi(e);
     if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
     if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
-    if (const char* e = getenv("ICP_NN_CTAS")) c->forced_ctas = atoi(e);
-    if (const char* e = getenv("ICP_NN_MIN_UNITS")) c->min_units = atoi(e);
-    if ((r = set_identity_xf(c))) { icp_destroy(c); return r; }
+    return set_identity_xf(c);
+}
+
+int icp_create(icp_ctx** out, int device)
+{
+    if (!out) return ICP_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+        g_err = "no usable CUDA device (this library has no CPU fallback)";
+        cudaGetLastError();
+        return ICP_ERR_NO_DEVICE;
+    }
+    icp_ctx* c = new icp_ctx();
+    c->device = device;
+    const int r = create_body(c, device);
+    if (r) {                                  // frees whatever was created so far; g_err keeps the cause
+        const std::string why = g_err;
+        icp_destroy(c);
+        g_err = why;
+        return r;
+    }
     *out = c;
     return ICP_OK;
 }
@@ -530,13 +457,13 @@ void icp_destroy(icp_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->st);
+    if (c->st) cudaStreamSynchronize(c->st);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (int r = 0; r < c->peer.world; ++r)
         if (c->peer_ready && r != c->peer.rank && c->peer.box[r]) cudaIpcCloseMemHandle(c->peer.box[r]);
     dfree(c->d_mailbox); dfree(c->d_trace);
     if (c->h_progress) cudaFreeHost(c->h_progress);
-    dfree(c->m.m64x); dfree(c->m.m64y); dfree(c->m.m64z); dfree(c->m.mhat); dfree(c->m.geo);
+    dfree(c->m.m64); dfree(c->m.mhat); dfree(c->m.geo);
     dfree(c->s.p64x); dfree(c->s.p64y); dfree(c->s.p64z); dfree(c->s.q64x); dfree(c->s.q64y); dfree(c->s.q64z);
     dfree(c->s.phx); dfree(c->s.phy); dfree(c->s.phz); dfree(c->s.perm); dfree(c->s.idx);
     dfree(c->sc.best); dfree(c->sc.runner); dfree(c->sc.chunk); dfree(c->sc.amb_list); dfree(c->sc.amb_thr);
@@ -547,8 +474,6 @@ void icp_destroy(icp_ctx* c)
     if (c->tree.kd_scratch) cudaFree(c->tree.kd_scratch);
     if (c->d_cub) cudaFree(c->d_cub);
     for (auto e : c->ev_filter) cudaEventDestroy(e);
-    if (c->loop_graph) cudaGraphExecDestroy(c->loop_graph);
-    if (c->loop_graph_tmpl) cudaGraphDestroy(c->loop_graph_tmpl);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->st) cudaStreamDestroy(c->st);
@@ -565,9 +490,9 @@ int icp_set_model(icp_ctx* c, const double* m_xyz, int64_t nm)
     c->m.nm = nm;
     c->m.nm_pad = (nm + NN_TM - 1) / NN_TM * NN_TM;
     if (c->cap_nm < (size_t)c->m.nm_pad) {       // grow only: cudaFree/cudaMalloc synchronise the whole device
-        if ((r = dalloc(&c->m.m64x, (size_t)c->m.nm_pad)) || (r = dalloc(&c->m.m64y, (size_t)c->m.nm_pad)) ||
-            (r = dalloc(&c->m.m64z, (size_t)c->m.nm_pad)) || (r = dalloc(&c->m.mhat, (size_t)c->m.nm_pad)))
-            return r;
+        c->cap_nm = 0;
+        c->have_model = false;
+        if ((r = dalloc(&c->m.m64, (size_t)c->m.nm_pad)) || (r = dalloc(&c->m.mhat, (size_t)c->m.nm_pad))) return r;
         c->cap_nm = (size_t)c->m.nm_pad;
     }
     launch_bbox(c->d_stage, nm, c->m.geo + 4, c->d_partials, c->sm_count * 2, c->d_ctl, c->st);
@@ -576,7 +501,16 @@ int icp_set_model(icp_ctx* c, const double* m_xyz, int64_t nm)
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&c->h_Rm, c->m.geo + 3, sizeof(double), cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
+    if (!(c->h_Rm == c->h_Rm) || c->h_Rm > 1.7e308) {
+        // an infinite coordinate (or no finite point at all) leaves no finite bounding box: the FP32 shadow would be all
+        // NaN and every search would degenerate into np x nm FP64 evaluations.  NaN coordinates alone are tolerated
+        // (the bounding box ignores them; such a point is never a nearest neighbour, see nn_pass for index 0).
+        c->have_model = false;
+        g_err = "icp_set_model: the model has infinite coordinates (or no finite point)";
+        return ICP_ERR_INVALID;
+    }
     c->tree_built[0] = c->tree_built[1] = false;
+    c->model0_nan = m_xyz[0] != m_xyz[0] || m_xyz[1] != m_xyz[1] || m_xyz[2] != m_xyz[2];
     c->have_model = true;
     c->have_idx = false;
     c->stats.nm = nm;
@@ -844,8 +778,6 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     const int LA = (c->lookahead > 0 && !nccl_path(c)) ? (c->lookahead < 2 ? 2 : c->lookahead) : 0;   // >= 2: see nn_filter_kernel
     *(volatile int*)c->h_progress = 0;
     c->progress_arg = LA ? c->d_progress : nullptr;
-    // ICP_GRAPH (experiment): brute-force search only, no per-kernel profiling events, not on the NCCL path
-    bool use_graph = c->graph_mode > 0 && !c->profile && !nccl_path(c) && !tree_active(c);
     for (int it = 0; it < max_iter; ++it) {
         if (LA && it >= LA) {
             const int w = wait_progress(c, it + 1 - LA, it);
@@ -853,22 +785,6 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
             if (w) break;
         }
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
-        if (use_graph && it >= 1) {
-            // iteration 0 always takes the plain path (first-call attribute set-up, and its two events time the filter)
-            if (it == 1) {
-                icp_ctx::GraphKey key;
-                fill_graph_key(c, np_glob, threshold, key);
-                if ((!c->loop_graph || memcmp(&key, &c->graph_key, sizeof(key)) != 0) && !capture_iteration(c, np_glob, threshold))
-                    use_graph = false;
-            }
-            if (use_graph) {
-                CK(cudaGraphExecEventRecordNodeSetEvent(c->loop_graph, c->graph_ev_node[0], ev[0]));
-                CK(cudaGraphExecEventRecordNodeSetEvent(c->loop_graph, c->graph_ev_node[1], ev[1]));
-                CK(cudaGraphLaunch(c->loop_graph, c->st));
-                c->stats.kernels_launched += c->graph_kernels;
-                continue;
-            }
-        }
         nn_pass(c, 1, (it > 0 || c->have_idx) ? 1 : 0, ev[0], ev[1], c->profile ? ev[2] : nullptr, c->profile ? ev[3] : nullptr);
         if (!nccl_path(c)) {
             int launched = align_step(c, 1, 1, 1, np_glob, threshold);
@@ -892,7 +808,11 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     int ctl[CTL_N];
     CK(cudaMemcpyAsync(ctl, c->d_ctl, sizeof(ctl), cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
-    if (ctl[CTL_COMM_TIMEOUT]) { g_err = "peer exchange timed out (a rank did not arrive)"; return ICP_ERR_COMM; }
+    if (ctl[CTL_COMM_TIMEOUT]) {
+        g_err = "peer exchange timed out (a rank did not arrive); new_p holds the last completed iteration, the communicator is unusable";
+        return ICP_ERR_COMM;
+    }
+    if (ctl[CTL_BOUNDS]) { g_err = "bounds check failed at csrc line " + std::to_string(ctl[CTL_BOUNDS]); return ICP_ERR_CUDA; }
     const int iters = ctl[CTL_ITERS];
     if (iters_done) *iters_done = iters;
     if (err_hist && iters > 0)
@@ -901,7 +821,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->stats.nn_calls += iters;
     c->stats.nn_pairs += (int64_t)iters * c->s.np * c->m.nm;
     c->stats.rerank_full += ctl[CTL_AMB_TOTAL];
-    c->stats.rerank_chunk += ctl[CTL_CHUNK_TOTAL];
+    c->stats.rerank_chunk += (int64_t)iters * c->s.np - ctl[CTL_AMB_TOTAL];
     cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
     float f = 0.f, f_ref = 0.f, f_ex = 0.f, f_al = 0.f;
     for (int it = 0; it < iters; ++it) {
@@ -922,7 +842,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     return ICP_OK;
 }
 
-int icp_get_trace(icp_ctx* c, double out_us[8])
+int icp_get_trace(icp_ctx* c, double out_us[10])
 {
     if (!c || !out_us) return ICP_ERR_INVALID;
     CK(cudaSetDevice(c->device));
@@ -932,6 +852,8 @@ int icp_get_trace(icp_ctx* c, double out_us[8])
     for (int i = 0; i < 8; ++i) out_us[i] = t[i] >= t[0] ? (double)(t[i] - t[0]) * 1e-3 : 0.0;
     out_us[0] = t[0] >= t[8] ? (double)(t[0] - t[8]) * 1e-3 : -1.0;     // gap: end of K1 -> entry of block 0
     if (t[9] >= t[0]) out_us[7] = (double)(t[9] - t[0]) * 1e-3;         // exit of the LAST block instead of block 0
+    out_us[8] = t[10] >= t[0] ? (double)(t[10] - t[0]) * 1e-3 : 0.0;
+    out_us[9] = t[11] >= t[0] ? (double)(t[11] - t[0]) * 1e-3 : 0.0;
     return ICP_OK;
 }
 

@@ -17,26 +17,29 @@ namespace icpb {
 
 // ---- nearest-neighbour filter geometry ---------------------------------------------------------
 // The ICP_NN_* macros exist for A/B builds only (`make variants`, tools/filter_ab.sh: one library per variant,
-// selected at run time with ICP_B200_LIB); the product is the defaults, which every committed number refers to.
+// selected at run time with ICP_B200_LIB); the product is the defaults.  Round 2 measured the variants the static SASS
+// study of round 1 favoured (profiles/r02a_ab_summary.txt): 12 scene points per thread at 3 CTAs per SM, 128-point
+// chunks and the inner loop unrolled 8x replaced round 1's 8 / 4 / 64 / 2 (horse 0.795 -> 0.833 of the FP32 roofline,
+// 2^18 points 0.858 -> 0.903).
 #ifndef ICP_NN_R
-#define ICP_NN_R 8
+#define ICP_NN_R 12
 #endif
 #ifndef ICP_NN_G
-#define ICP_NN_G 64
+#define ICP_NN_G 128
 #endif
 #ifndef ICP_NN_Q_UNROLL
-#define ICP_NN_Q_UNROLL 2
+#define ICP_NN_Q_UNROLL 8
 #endif
 #ifndef ICP_NN_MIN_CTAS
-#define ICP_NN_MIN_CTAS 4
+#define ICP_NN_MIN_CTAS 3
 #endif
 constexpr int NN_THREADS = 128;                 // threads per CTA
-constexpr int NN_R       = ICP_NN_R;            // scene points register-blocked per thread (8)
-constexpr int NN_TILE    = NN_THREADS * NN_R;   // scene points per CTA (1024)
-constexpr int NN_G       = ICP_NN_G;            // model points per tracking chunk (64)
+constexpr int NN_R       = ICP_NN_R;            // scene points register-blocked per thread (12)
+constexpr int NN_TILE    = NN_THREADS * NN_R;   // scene points per CTA (1536)
+constexpr int NN_G       = ICP_NN_G;            // model points per tracking chunk (128)
 constexpr int NN_TM      = 512;                 // model points per shared-memory stage
-constexpr int NN_Q_UNROLL = ICP_NN_Q_UNROLL;    // LDS.128 quadruples per trip of the filter's inner loop (2)
-constexpr int NN_MIN_CTAS = ICP_NN_MIN_CTAS;    // resident filter CTAs per SM the launch bounds ask for (4)
+constexpr int NN_Q_UNROLL = ICP_NN_Q_UNROLL;    // LDS.128 quadruples per trip of the filter's inner loop (8)
+constexpr int NN_MIN_CTAS = ICP_NN_MIN_CTAS;    // resident filter CTAs per SM the launch bounds ask for (3)
 static_assert(NN_TM % NN_G == 0 && NN_G % 32 == 0 && NN_G <= 256, "chunk size");
 static_assert((NN_G / 4) % NN_Q_UNROLL == 0, "inner-loop unroll must divide the chunk");
 constexpr float NN_SENTINEL = 1.0e18f;          // coordinate of padded model points (never wins)
@@ -48,7 +51,9 @@ constexpr int XF_N  = 20;   // s, R[9], t[3], mu_p[3], mu_y[3], spare
 
 // ctl[] slots (int32, device)
 enum { CTL_DONE = 0, CTL_ITERS = 1, CTL_AMB_COUNT = 2, CTL_TICKET_MOM = 3, CTL_TICKET_ERR = 4,
-       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6, CTL_TICKET_NN = 7, CTL_COMM_TIMEOUT = 8, CTL_TICKET_BBOX = 9, CTL_N = 12 };
+       CTL_AMB_TOTAL = 5, CTL_CHUNK_TOTAL = 6 /* unused: derived on the host */, CTL_TICKET_NN = 7, CTL_COMM_TIMEOUT = 8,
+       CTL_TICKET_BBOX = 9, CTL_BOUNDS = 10 /* checked builds (ICP_BOUNDS_CHECK): source line of the first bad gather index */,
+       CTL_N = 12 };
 
 // ---- peer-memory exchange (multi-GPU, one process per GPU) ---------------------------------------
 // Every rank owns one mailbox in its HBM, mapped into all peers through CUDA IPC.  The exchange number q is kept
@@ -69,9 +74,15 @@ struct PeerComm {
     int rank = 0, world = 0;                        // world == 0: no peers attached (single GPU)
 };
 
+// FP64 model master: one 32-byte record per point (x, y, z, 0).  Every FP64 use of the model is a GATHER through a
+// correspondence index (K1's re-rank, K2, K4, the exports), so one point = one 32-byte DRAM sector = one LDG.256;
+// the SoA layout of round 1 cost three sectors for 24 useful bytes (ncu, 2^22 points: K2 read 113 B per point for 52
+// algorithmic, profiles/r02a_syn4m_k2k4_split_metrics.csv).
+struct __align__(32) Pt64 { double x, y, z, w; };
+
 struct ModelDev {
     int64_t nm = 0, nm_pad = 0;
-    double *m64x = nullptr, *m64y = nullptr, *m64z = nullptr;
+    Pt64* m64 = nullptr;
     float4* mhat = nullptr;
     double* geo = nullptr;       // device: c0[3], Rm (upper bound of |m - c0|), bbox min[3], max[3]
 };
@@ -125,8 +136,9 @@ struct TreeDev {
 // when ctl[CTL_DONE] != 0 and `honor_done` is set (used by the device-side loop).
 void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc, const int* ctl, int honor_done,
                       cudaStream_t st, int* progress = nullptr);
+// inline_exact: the refine kernel rescans the model itself for the points it cannot decide (no nn_exact launch needed)
 void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
-                      cudaStream_t st);
+                      int inline_exact, cudaStream_t st);
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                      int sm_count, cudaStream_t st, unsigned long long* trace = nullptr);
 int nn_exact_batch_points();
@@ -184,6 +196,31 @@ int reduce_blocks_for(int64_t n, int sm_count);
 
 // ---- small device helpers -----------------------------------------------------------------------
 #ifdef __CUDACC__
+// one model point of the FP64 master: a single 256-bit read-only load (SASS LDG.E.ENL2.256.CONSTANT)
+__device__ __forceinline__ void ld_pt64(const Pt64* __restrict__ a, int k, double& x, double& y, double& z)
+{
+    double w __attribute__((unused));
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(x), "=d"(y), "=d"(z), "=d"(w) : "l"(a + k));
+}
+// A scene point with a NaN or infinite coordinate has only NaN / +inf distances; Eigen's minCoeff visitor starts at
+// column 0 and only moves on a strict `<` (src/cpu.cc:21-22), so the reference matches it to index 0.  Every search
+// kernel answers that directly instead of scanning the model for it (after one such iteration the reference's
+// transform is NaN and EVERY scene point is of this kind).
+__device__ __forceinline__ bool scene_point_finite(double x, double y, double z)
+{
+    return isfinite(x) && isfinite(y) && isfinite(z);
+}
+// Checked builds (make checked: -DICP_BOUNDS_CHECK, the stand-in for compute-sanitizer, which is closed on this pool):
+// every gather index is range-checked; the first offender's source line lands in ctl[CTL_BOUNDS] and the index is
+// clamped, so a test run under the checked library fails loudly instead of faulting.
+#ifdef ICP_BOUNDS_CHECK
+#define ICP_CHK_IDX(k, n, ctl)                                                              \
+    do {                                                                                    \
+        if ((unsigned)(k) >= (unsigned)(n)) { atomicCAS((int*)&(ctl)[CTL_BOUNDS], 0, __LINE__); (k) = 0; } \
+    } while (0)
+#else
+#define ICP_CHK_IDX(k, n, ctl) do { } while (0)
+#endif
 // Loop progress for the host (icp_run keeps only a few iterations enqueued ahead of the device): `progress`
 // points into mapped pinned host memory, one word = (iterations closed << 1) | converged.  Called at the entry of
 // the FIRST kernel of an iteration, so that the PCIe write drains under that kernel instead of at a kernel end.

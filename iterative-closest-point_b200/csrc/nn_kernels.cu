@@ -249,10 +249,11 @@ __device__ __forceinline__ double dist2_64(double px, double py, double pz, doub
 // Running first-minimum of v = sqrt(s) over ascending indices, exactly as Eigen's minCoeff sees the
 // reference's d(k) = sqrt(...) (src/cpu.cc:19-22), but evaluating the sqrt only when s improves:
 // sqrt is monotone, so s >= s_best can never give a strictly smaller v.
+constexpr int NO_INDEX = 0x7fffffff;
 struct Best64 {
     double s, v;
     int k;
-    __device__ __forceinline__ void init() { s = v = __longlong_as_double(0x7ff0000000000000LL); k = 0x7fffffff; }
+    __device__ __forceinline__ void init() { s = v = __longlong_as_double(0x7ff0000000000000LL); k = NO_INDEX; }
     __device__ __forceinline__ void feed(double s_new, int k_new)   // k_new > k of everything fed before
     {
         if (s_new < s) {
@@ -262,6 +263,10 @@ struct Best64 {
         }
     }
 };
+// Nothing was ever accepted: every distance of the row is +inf or NaN (a non-finite scene point, or one so far away
+// that the FP64 squares overflow).  Eigen's minCoeff visitor starts at column 0 and only moves on a strict `<`
+// (src/cpu.cc:21-22), so the reference's answer is index 0.
+__device__ __forceinline__ int first_min_or_zero(int k) { return k == NO_INDEX ? 0 : k; }
 
 // lexicographic (value, index) minimum over `width` adjacent lanes: lowest index wins ties
 template <int WIDTH>
@@ -286,40 +291,134 @@ __device__ __forceinline__ float surrogate32(const float4 mh, float cx, float cy
     return __fmaf_rn(ax, x, __fmaf_rn(ay, y, __fmaf_rn(az, z, w)));
 }
 
-constexpr int REFINE_THREADS = 256;
+// ---- block-cooperative exact scan (shared by nn_refine's in-kernel path and nn_exact) ---------------------------
+// A block of SCAN_THREADS threads rescans model points [k_begin, k_end) for P undecided scene points at once: FP32
+// surrogate against each point's acceptance threshold; every survivor (a superset of the reference's possible argmins)
+// gets the reference's FP64 expression; first minimum wins.  A model point is loaded once for the P points.
+constexpr int SCAN_THREADS = 256;
+constexpr int EX_U = 4;          // model points in flight per thread
+struct ScanPoint { float cx, cy, cz, ax, ay, az, thr; };
+
+__device__ __forceinline__ ScanPoint scan_point(const float* __restrict__ phx, const float* __restrict__ phy,
+                                                const float* __restrict__ phz, int j, float thr)
+{
+    ScanPoint q;
+    const int cj = (j / NN_TILE) * NN_TILE + NN_TILE / 2;
+    q.cx = phx[cj]; q.cy = phy[cj]; q.cz = phz[cj];
+    q.ax = -2.0f * __fsub_rn(phx[j], q.cx);
+    q.ay = -2.0f * __fsub_rn(phy[j], q.cy);
+    q.az = -2.0f * __fsub_rn(phz[j], q.cz);
+    q.thr = thr;
+    return q;
+}
+
+template <int P>
+__device__ __forceinline__ void scan_model(const float4* __restrict__ mhat, const Pt64* __restrict__ m64, int nm_pad,
+                                           int k_begin, int k_end, const ScanPoint (&q)[P], const double (*sp)[3],
+                                           Best64 (&bt)[P])
+{
+    for (int kb = k_begin + (int)threadIdx.x; kb < k_end; kb += SCAN_THREADS * EX_U) {
+        float4 mh[EX_U];
+#pragma unroll
+        for (int u = 0; u < EX_U; ++u) mh[u] = mhat[min(kb + u * SCAN_THREADS, nm_pad - 1)];
+#pragma unroll
+        for (int u = 0; u < EX_U; ++u) {
+            const int kk = kb + u * SCAN_THREADS;
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const float d = surrogate32(mh[u], q[p].cx, q[p].cy, q[p].cz, q[p].ax, q[p].ay, q[p].az);
+                if (!(d > q[p].thr) && kk < k_end) {
+                    double mx, my, mz;
+                    ld_pt64(m64, kk, mx, my, mz);
+                    bt[p].feed(dist2_64(sp[p][0], sp[p][1], sp[p][2], mx, my, mz), kk);
+                }
+            }
+        }
+    }
+}
+
+// (value, index) minimum of the block's P running minima; the result is valid in thread 0.  Ends with a barrier, so
+// sv / sk may be reused right after.
+template <int P>
+__device__ __forceinline__ void block_argmin(const Best64 (&bt)[P], double (*sv)[SCAN_THREADS / 32],
+                                             int (*sk)[SCAN_THREADS / 32], double (&v_out)[P], int (&k_out)[P])
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        double v = bt[p].v;
+        int k = bt[p].k;
+        group_argmin<32>(v, k);
+        if (lane == 0) { sv[p][w] = v; sk[p][w] = k; }
+    }
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            double v = lane < SCAN_THREADS / 32 ? sv[p][lane] : __longlong_as_double(0x7ff0000000000000LL);
+            int k = lane < SCAN_THREADS / 32 ? sk[p][lane] : NO_INDEX;
+            group_argmin<32>(v, k);
+            v_out[p] = v;
+            k_out[p] = k;
+        }
+    }
+    __syncthreads();
+}
+
+constexpr int REFINE_THREADS = SCAN_THREADS;
 #ifndef ICP_RF
 #define ICP_RF 8
 #endif
 constexpr int RF = ICP_RF;    // lanes cooperating on one scene point (8; build-time variant like ICP_NN_*)
 static_assert(RF == 4 || RF == 8 || RF == 16, "RF");
 static_assert(NN_G / RF <= 32, "nn_refine keeps one candidate bit per (lane, step) of the best chunk in a 32-bit mask");
+constexpr int RF_PPW = 32 / RF;                              // scene points per warp
+constexpr int RF_PPB = (REFINE_THREADS / 32) * RF_PPW;       // scene points per block and trip (32)
+#ifndef ICP_IN_P
+#define ICP_IN_P 2
+#endif
+constexpr int IN_P = ICP_IN_P;  // undecided points per in-kernel scan of nn_refine
 
 // nn_refine: merges the model splits, derives the bound tau and the FP32 acceptance threshold
 // thr = best + tau (rounded up).  Every model point that can be the reference's argmin has d' <= thr.
-//  - runner > thr ("clear"): all such points lie in the best chunk.  Its 64 points are re-scored with the
+//  - runner > thr ("clear"): all such points lie in the best chunk.  Its NN_G points are re-scored with the
 //    FP32 surrogate; only those with d' <= thr (typically one) are evaluated in FP64 with the
 //    reference's own expression, first minimum wins.
-//  - otherwise the point is queued with its threshold for nn_exact (FP32 rescan of the whole model).
-__global__ void __launch_bounds__(REFINE_THREADS)
-nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
-                 const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
+//  - otherwise the point is undecided and the WHOLE model is rescanned against its threshold:
+//      inline_exact = 1 (models up to 131 072 points): right here, by the block that met the point (round 1 queued
+//        these for a separate kernel: on horse that launch served ~85 points per pass and cost 20 us of the 370 us
+//        iteration; the in-kernel scan of 48 485 model points by 256 threads takes ~2 us and only delays its own block);
+//      inline_exact = 0 (large models, where a scan is worth sharing between points of different blocks): the point is
+//        queued with its threshold for nn_exact.
+__global__ void __launch_bounds__(REFINE_THREADS, 4)
+nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, int nm_pad,
+                 const double* __restrict__ geo,
                  const double* __restrict__ p64x, const double* __restrict__ p64y, const double* __restrict__ p64z,
                  const float* __restrict__ phx, const float* __restrict__ phy, const float* __restrict__ phz, int np,
                  int np_pad, int n_tiles, int cpt, int n_cta, const float* __restrict__ part_best,
                  const float* __restrict__ part_runner,
                  const uint32_t* __restrict__ part_chunk, int32_t* __restrict__ idx, int32_t* __restrict__ amb_list,
-                 float* __restrict__ amb_thr, int* __restrict__ ctl, int honor_done)
+                 float* __restrict__ amb_thr, int* __restrict__ ctl, int honor_done, int inline_exact)
 {
     if (honor_done && ctl[CTL_DONE]) return;
-    const int lane = threadIdx.x & 31, sub = lane & (RF - 1), grp = lane / RF;
-    const int warp = (blockIdx.x * REFINE_THREADS + threadIdx.x) >> 5;
-    const int n_warps = (gridDim.x * REFINE_THREADS) >> 5;
-    constexpr int PPW = 32 / RF;                       // scene points per warp
+    __shared__ int s_cnt;
+    __shared__ int s_j[RF_PPB];
+    __shared__ float s_thr[RF_PPB];
+    __shared__ double sp[IN_P][3];
+    __shared__ double sv[IN_P][SCAN_THREADS / 32];
+    __shared__ int sk[IN_P][SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, sub = lane & (RF - 1), grp = lane / RF, w = threadIdx.x >> 5;
     const float Rm = __double2float_ru(geo[3]);
     const float INF = __int_as_float(0x7f800000);
     const unsigned gmask = ((1u << RF) - 1u) << (grp * RF);
+    int undecided = 0;                                 // thread 0: points this block rescanned itself
 
-    for (int jb = warp * PPW; jb < np; jb += n_warps * PPW) {
+    for (int base = blockIdx.x * RF_PPB; base < np; base += gridDim.x * RF_PPB) {      // block-uniform trip count
+        if (inline_exact) {
+            if (threadIdx.x == 0) s_cnt = 0;
+            __syncthreads();
+        }
+        const int jb = base + w * RF_PPW;
         const bool valid = jb + grp < np;
         const int j = valid ? jb + grp : np - 1;
         // everything the point needs, requested up front so the latencies overlap
@@ -348,7 +447,7 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         if (__popc(eq) > 1 && best < INF) runner = best;
 #pragma unroll
         for (int o = RF / 2; o > 0; o >>= 1) runner = fminf(runner, __shfl_xor_sync(0xffffffffu, runner, o));
-        const uint32_t chunk = __shfl_sync(0xffffffffu, ch, grp * RF + src);
+        const uint32_t chunk = __shfl_sync(0xffffffffu, ch, grp * RF + max(src, 0));
 
         // ---- rigorous error bound, evaluated in FP32 with every operation rounded UP (all terms are
         //      non-negative, so the result is >= the real-valued formula of DESIGN.md §K1) --------------
@@ -374,7 +473,9 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
         const float thr = __fadd_ru(best, tau);                       // NaN / +inf: everything is a candidate
         const bool clear = runner > thr && thr < INF;                 // false for NaN/inf oddities too
 
-        if (clear) {
+        if (!scene_point_finite(px, py, pz)) {        // uniform per group: the reference's answer is index 0
+            if (sub == 0 && valid) idx[j] = 0;
+        } else if (clear) {
             // ---- best chunk: FP32 surrogate against thr, FP64 only for the survivors ---------------
             const float ax = -2.0f * lx, ay = -2.0f * ly, az = -2.0f * lz;
             const int k0 = (int)chunk * NN_G;
@@ -389,27 +490,72 @@ nn_refine_kernel(const double* __restrict__ m64x, const double* __restrict__ m64
             while (cand) {                           // ascending i = ascending model index
                 const int i = __ffs(cand) - 1;
                 cand &= cand - 1u;
-                const int kk = k0 + i * RF + sub;
-                bt.feed(dist2_64(px, py, pz, m64x[kk], m64y[kk], m64z[kk]), kk);
+                int kk = k0 + i * RF + sub;
+                ICP_CHK_IDX(kk, nm, ctl);
+                double mx, my, mz;
+                ld_pt64(m64, kk, mx, my, mz);
+                bt.feed(dist2_64(px, py, pz, mx, my, mz), kk);
             }
             double v = bt.v;
             int k = bt.k;
             group_argmin<RF>(v, k, gmask);             // `clear` is uniform per group, not per warp
-            if (sub == 0 && valid) idx[j] = k;
+            if (sub == 0 && valid) idx[j] = first_min_or_zero(k);
         } else if (sub == 0 && valid) {
-            const int pos = atomicAdd(&ctl[CTL_AMB_COUNT], 1);
-            amb_list[pos] = j;
-            amb_thr[pos] = thr;
+            if (inline_exact) {
+                const int pos = atomicAdd(&s_cnt, 1);
+                s_j[pos] = j;
+                s_thr[pos] = thr;
+            } else {
+                const int pos = atomicAdd(&ctl[CTL_AMB_COUNT], 1);
+                amb_list[pos] = j;
+                amb_thr[pos] = thr;
+            }
+        }
+
+        if (inline_exact) {
+            // ---- the block rescans the whole model for the points of this trip it could not decide ----
+            __syncthreads();
+            const int nq = s_cnt;                    // block-uniform
+            for (int a0 = 0; a0 < nq; a0 += IN_P) {
+                ScanPoint q[IN_P];
+#pragma unroll
+                for (int p = 0; p < IN_P; ++p) {
+                    const int a = min(a0 + p, nq - 1);          // ragged last batch: duplicates, results dropped
+                    q[p] = scan_point(phx, phy, phz, s_j[a], s_thr[a]);
+                }
+                if (threadIdx.x < IN_P) {
+                    const int jq = s_j[min(a0 + (int)threadIdx.x, nq - 1)];
+                    sp[threadIdx.x][0] = p64x[jq];
+                    sp[threadIdx.x][1] = p64y[jq];
+                    sp[threadIdx.x][2] = p64z[jq];
+                }
+                __syncthreads();
+                Best64 bt[IN_P];
+#pragma unroll
+                for (int p = 0; p < IN_P; ++p) bt[p].init();
+                scan_model<IN_P>(mhat, m64, nm_pad, 0, nm, q, sp, bt);
+                double v[IN_P];
+                int k[IN_P];
+                block_argmin<IN_P>(bt, sv, sk, v, k);
+                if (threadIdx.x == 0) {
+#pragma unroll
+                    for (int p = 0; p < IN_P; ++p)
+                        if (a0 + p < nq) idx[s_j[a0 + p]] = first_min_or_zero(k[p]);
+                }
+            }
+            if (threadIdx.x == 0) undecided += nq;
+            __syncthreads();                         // s_j / s_cnt are rewritten by the next trip
         }
     }
+    if (inline_exact && threadIdx.x == 0 && undecided > 0) atomicAdd(&ctl[CTL_AMB_TOTAL], undecided);
 }
 
-// nn_exact: the scene points the chunk test could not decide.  FP32 rescan of the WHOLE model with the
+// nn_exact (large models only, see nn_refine): the queued scene points.  FP32 rescan of the WHOLE model with the
 // filter's surrogate; every model point with d' <= thr (a superset of the reference's possible argmins)
 // is evaluated in FP64 with the reference's expression; first minimum wins.
 // Work item = (batch of EX_P queued points) x (model segment); a model point is loaded once per batch.
 // Segment results are merged by the last CTA to finish a batch (ticket per batch).
-constexpr int EXACT_THREADS = 256;
+constexpr int EXACT_THREADS = SCAN_THREADS;
 #ifndef ICP_EX_P
 #define ICP_EX_P 4
 #endif
@@ -417,12 +563,11 @@ constexpr int EXACT_THREADS = 256;
 #define ICP_EX_MIN_SEG 4096
 #endif
 constexpr int EX_P = ICP_EX_P;   // queued points per batch (4; build-time variant like ICP_NN_*)
-constexpr int EX_U = 4;          // model points in flight per thread
 constexpr int EX_MIN_SEG = ICP_EX_MIN_SEG; // model points per segment at least (4096; 1024 was measured slower: more tickets and merges)
 
 __global__ void __launch_bounds__(EXACT_THREADS)
-nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y, const double* __restrict__ m64z,
-                const float4* __restrict__ mhat, int nm, int nm_pad, const double* __restrict__ p64x,
+nn_exact_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, int nm_pad,
+                const double* __restrict__ p64x,
                 const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
                 const float* __restrict__ phy, const float* __restrict__ phz, const int32_t* __restrict__ amb_list,
                 const float* __restrict__ amb_thr, int32_t* __restrict__ idx, double* __restrict__ seg_v,
@@ -435,7 +580,6 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
     __shared__ int sk[EX_P][EXACT_THREADS / 32];
     __shared__ int s_last;
     const int count = ctl[CTL_AMB_COUNT];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int n_batches = (count + EX_P - 1) / EX_P;
     // segments: enough items to fill the grid twice, bounded by the segment floor and the scratch
     int n_seg = 1;
@@ -452,20 +596,14 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
         const int batch = item / n_seg, seg = item - batch * n_seg;
         const int a0 = batch * EX_P;
         int jj[EX_P];
-        float cx[EX_P], cy[EX_P], cz[EX_P], ax[EX_P], ay[EX_P], az[EX_P], thr[EX_P];
+        ScanPoint q[EX_P];
 #pragma unroll
         for (int p = 0; p < EX_P; ++p) {
             const int a = min(a0 + p, count - 1);          // ragged last batch: duplicates, results dropped
-            const int j = amb_list[a];
-            jj[p] = j;
-            thr[p] = amb_thr[a];
-            const int cj = (j / NN_TILE) * NN_TILE + NN_TILE / 2;
-            cx[p] = phx[cj]; cy[p] = phy[cj]; cz[p] = phz[cj];
-            ax[p] = -2.0f * __fsub_rn(phx[j], cx[p]);
-            ay[p] = -2.0f * __fsub_rn(phy[j], cy[p]);
-            az[p] = -2.0f * __fsub_rn(phz[j], cz[p]);
+            jj[p] = amb_list[a];
+            q[p] = scan_point(phx, phy, phz, jj[p], amb_thr[a]);
         }
-        __syncthreads();                                    // previous item's readers of sp/sv/sk are done
+        __syncthreads();                                    // previous item's readers of sp are done
         if (threadIdx.x < EX_P) {
             const int j = amb_list[min(a0 + (int)threadIdx.x, count - 1)];
             sp[threadIdx.x][0] = p64x[j];
@@ -477,40 +615,17 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
 #pragma unroll
         for (int p = 0; p < EX_P; ++p) bt[p].init();
         const int k_begin = seg * seg_len, k_end = min(k_begin + seg_len, nm);
-        for (int kb = k_begin + (int)threadIdx.x; kb < k_end; kb += EXACT_THREADS * EX_U) {
-            float4 mh[EX_U];
+        scan_model<EX_P>(mhat, m64, nm_pad, k_begin, k_end, q, sp, bt);
+        double v[EX_P];
+        int k[EX_P];
+        block_argmin<EX_P>(bt, sv, sk, v, k);
+        if (threadIdx.x == 0) {
 #pragma unroll
-            for (int u = 0; u < EX_U; ++u) mh[u] = mhat[min(kb + u * EXACT_THREADS, nm_pad - 1)];
-#pragma unroll
-            for (int u = 0; u < EX_U; ++u) {
-                const int kk = kb + u * EXACT_THREADS;
-#pragma unroll
-                for (int p = 0; p < EX_P; ++p) {
-                    const float d = surrogate32(mh[u], cx[p], cy[p], cz[p], ax[p], ay[p], az[p]);
-                    if (!(d > thr[p]) && kk < k_end)
-                        bt[p].feed(dist2_64(sp[p][0], sp[p][1], sp[p][2], m64x[kk], m64y[kk], m64z[kk]), kk);
+            for (int p = 0; p < EX_P; ++p)
+                if (a0 + p < count) {
+                    if (n_seg == 1) idx[jj[p]] = first_min_or_zero(k[p]);
+                    else { seg_v[(size_t)seg * n_batches * EX_P + a0 + p] = v[p]; seg_k[(size_t)seg * n_batches * EX_P + a0 + p] = k[p]; }
                 }
-            }
-        }
-#pragma unroll
-        for (int p = 0; p < EX_P; ++p) {
-            double v = bt[p].v;
-            int k = bt[p].k;
-            group_argmin<32>(v, k);
-            if (lane == 0) { sv[p][w] = v; sk[p][w] = k; }
-        }
-        __syncthreads();
-        if (w == 0) {
-#pragma unroll
-            for (int p = 0; p < EX_P; ++p) {
-                double v = lane < EXACT_THREADS / 32 ? sv[p][lane] : DINF;
-                int k = lane < EXACT_THREADS / 32 ? sk[p][lane] : 0x7fffffff;
-                group_argmin<32>(v, k);
-                if (lane == 0 && a0 + p < count) {
-                    if (n_seg == 1) idx[jj[p]] = k;
-                    else { seg_v[(size_t)seg * n_batches * EX_P + a0 + p] = v; seg_k[(size_t)seg * n_batches * EX_P + a0 + p] = k; }
-                }
-            }
         }
         if (n_seg > 1) {
             if (threadIdx.x == 0) {
@@ -522,14 +637,14 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
             __syncthreads();
             if (s_last && threadIdx.x < EX_P && a0 + (int)threadIdx.x < count) {
                 __threadfence();
-                double v = DINF;
-                int k = 0x7fffffff;
+                double vm = DINF;
+                int km = NO_INDEX;
                 for (int s = 0; s < n_seg; ++s) {
-                    const double ov = seg_v[(size_t)s * n_batches * EX_P + a0 + threadIdx.x];
-                    const int ok = seg_k[(size_t)s * n_batches * EX_P + a0 + threadIdx.x];
-                    if (ov < v || (ov == v && ok < k)) { v = ov; k = ok; }
+                    const double ov = __ldcg(&seg_v[(size_t)s * n_batches * EX_P + a0 + threadIdx.x]);
+                    const int ok = __ldcg(&seg_k[(size_t)s * n_batches * EX_P + a0 + threadIdx.x]);
+                    if (ov < vm || (ov == vm && ok < km)) { vm = ov; km = ok; }
                 }
-                idx[amb_list[a0 + threadIdx.x]] = k;
+                idx[amb_list[a0 + threadIdx.x]] = first_min_or_zero(km);
             }
         }
     }
@@ -537,7 +652,6 @@ nn_exact_kernel(const double* __restrict__ m64x, const double* __restrict__ m64y
         __threadfence();
         if (atomicAdd(&ctl[CTL_TICKET_NN], 1) == (int)gridDim.x - 1) {
             ctl[CTL_AMB_TOTAL] += count;
-            ctl[CTL_CHUNK_TOTAL] += np - count;
             ctl[CTL_AMB_COUNT] = 0;
             ctl[CTL_TICKET_NN] = 0;
             if (trace) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(trace[8]));   // diagnostic: last block of K1 done
@@ -561,24 +675,23 @@ void launch_nn_filter(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
 }
 
 void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
-                      cudaStream_t st)
+                      int inline_exact, cudaStream_t st)
 {
-    const int64_t warps = (s.np + 32 / RF - 1) / (32 / RF);
-    int grid = (int)((warps * 32 + REFINE_THREADS - 1) / REFINE_THREADS);
+    int64_t grid = (s.np + RF_PPB - 1) / RF_PPB;
     if (grid > 148 * 16) grid = 148 * 16;
     if (grid < 1) grid = 1;
-    nn_refine_kernel<<<grid, REFINE_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.mhat, (int)m.nm, m.geo, s.p64x, s.p64y,
-                                                      s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)s.np_pad,
-                                                      (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.n_cta,
-                                                      sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list,
-                                                      sc.amb_thr, ctl, honor_done);
+    nn_refine_kernel<<<(int)grid, REFINE_THREADS, 0, st>>>(m.m64, m.mhat, (int)m.nm, (int)m.nm_pad, m.geo, s.p64x, s.p64y,
+                                                           s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)s.np_pad,
+                                                           (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.n_cta,
+                                                           sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list,
+                                                           sc.amb_thr, ctl, honor_done, inline_exact);
 }
 
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done, int sm_count,
                      cudaStream_t st, unsigned long long* trace)
 {
     const int grid = sm_count * 4;
-    nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64x, m.m64y, m.m64z, m.mhat, (int)m.nm, (int)m.nm_pad, s.p64x,
+    nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64, m.mhat, (int)m.nm, (int)m.nm_pad, s.p64x,
                                                     s.p64y, s.p64z, s.phx, s.phy, s.phz, sc.amb_list, sc.amb_thr, s.idx,
                                                     sc.seg_v, sc.seg_k, (int)sc.seg_cap, sc.batch_ticket, ctl,
                                                     (int)s.np, honor_done, trace);

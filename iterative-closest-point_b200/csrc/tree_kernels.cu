@@ -37,6 +37,12 @@ __device__ __forceinline__ double ref_dist2(double px, double py, double pz, dou
     const double dx = __dsub_rn(px, mx), dy = __dsub_rn(py, my), dz = __dsub_rn(pz, mz);
     return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
+__device__ __forceinline__ double ref_dist2_pt(double px, double py, double pz, const Pt64* __restrict__ m64, int k)
+{
+    double mx, my, mz;
+    ld_pt64(m64, k, mx, my, mz);
+    return ref_dist2(px, py, pz, mx, my, mz);
+}
 
 __device__ __forceinline__ uint32_t tree_spread10(uint32_t v)
 {
@@ -130,7 +136,7 @@ struct TreeQuery {
     float best2, thr2;       // running surrogate minimum and acceptance threshold
     double v;                // running reference minimum (v, k), lexicographic
     int k;
-    const double *m64x, *m64y, *m64z;
+    const Pt64* m64;
 
     __device__ __forceinline__ void set_best(float b2)
     {
@@ -143,7 +149,7 @@ struct TreeQuery {
     {
         if (d2 <= thr2) {
             if (d2 < best2) set_best(d2);
-            const double vv = __dsqrt_rn(ref_dist2(qx, qy, qz, m64x[kk], m64y[kk], m64z[kk]));
+            const double vv = __dsqrt_rn(ref_dist2_pt(qx, qy, qz, m64, kk));
             if (vv < v || (vv == v && kk < k)) { v = vv; k = kk; }
         }
     }
@@ -164,8 +170,7 @@ __device__ __forceinline__ float surrogate_direct(float px, float py, float pz, 
 // 40 registers: 40 instead of 48 resident warps per SM).
 __global__ void __launch_bounds__(TREE_THREADS)
 nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, int n_leaves /* power of two */,
-               const float4* __restrict__ mhat, const double* __restrict__ m64x, const double* __restrict__ m64y,
-               const double* __restrict__ m64z, const double* __restrict__ geo, const double* __restrict__ p64x,
+               const float4* __restrict__ mhat, const Pt64* __restrict__ m64, const double* __restrict__ geo, const double* __restrict__ p64x,
                const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
                const float* __restrict__ phy, const float* __restrict__ phz, int np, int nm,
                int32_t* __restrict__ idx, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
@@ -178,7 +183,8 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
     TreeQuery q;
     q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
     q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
-    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    q.m64 = m64;
+    if (!scene_point_finite(q.qx, q.qy, q.qz)) { idx[j] = 0; return; }
     {
         const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
         const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
@@ -238,7 +244,7 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
         double bv = __longlong_as_double(0x7ff0000000000000LL);
         q.k = 0;
         for (int kk = 0; kk < nm; ++kk) {
-            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+            const double vv = __dsqrt_rn(ref_dist2_pt(q.qx, q.qy, q.qz, m64, kk));
             if (vv < bv) { bv = vv; q.k = kk; }
         }
     }
@@ -458,8 +464,7 @@ __global__ void wtree_level_kernel(const float* __restrict__ lower, int n_upper,
 
 __global__ void __launch_bounds__(WT_WARPS * 32)
 nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __restrict__ pts,
-                const float4* __restrict__ mhat, const double* __restrict__ m64x, const double* __restrict__ m64y,
-                const double* __restrict__ m64z, const double* __restrict__ geo, const double* __restrict__ p64x,
+                const float4* __restrict__ mhat, const Pt64* __restrict__ m64, const double* __restrict__ geo, const double* __restrict__ p64x,
                 const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
                 const float* __restrict__ phy, const float* __restrict__ phz, int np, int nm,
                 int32_t* __restrict__ idx, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
@@ -474,7 +479,11 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     TreeQuery q;                                            // warp-uniform except (v, k), which are per lane
     q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
     q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
-    q.m64x = m64x; q.m64y = m64y; q.m64z = m64z;
+    q.m64 = m64;
+    if (!scene_point_finite(q.qx, q.qy, q.qz)) {            // warp-uniform
+        if (lane == 0) idx[j] = 0;
+        return;
+    }
     {
         const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
         const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
@@ -490,7 +499,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
             const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
             q.set_best(d2);
             if (lane == 0) {
-                q.v = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kp], m64y[kp], m64z[kp]));
+                q.v = __dsqrt_rn(ref_dist2_pt(q.qx, q.qy, q.qz, m64, kp));
                 q.k = kp;
             }
         }
@@ -531,7 +540,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
             if (dmin < q.best2) q.set_best(dmin);
             if (d2 <= q.thr2) {
                 const int kk = __float_as_int(m.w);
-                const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+                const double vv = __dsqrt_rn(ref_dist2_pt(q.qx, q.qy, q.qz, m64, kk));
                 if (vv < q.v || (vv == q.v && kk < q.k)) { q.v = vv; q.k = kk; }
             }
             rem &= ~(1u << c) & __ballot_sync(FULL, d <= q.thr2);
@@ -549,7 +558,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     if (k == 0x7fffffff) {       // FP32 surrogate overflowed (scene point > 1e19 away): FP64 scan, first minimum
         v = __longlong_as_double(0x7ff0000000000000LL);
         for (int kk = lane; kk < nm; kk += 32) {
-            const double vv = __dsqrt_rn(ref_dist2(q.qx, q.qy, q.qz, m64x[kk], m64y[kk], m64z[kk]));
+            const double vv = __dsqrt_rn(ref_dist2_pt(q.qx, q.qy, q.qz, m64, kk));
             if (vv < v) { v = vv; k = kk; }
         }
 #pragma unroll
@@ -674,22 +683,15 @@ void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int
                      cudaStream_t st, int* progress)
 {
     const int grid = (int)((s.np + WT_WARPS - 1) / WT_WARPS);
-    nn_wtree_kernel<<<grid, WT_WARPS * 32, 0, st>>>(t.wboxes, t.w, t.wpts, m.mhat, m.m64x, m.m64y, m.m64z, m.geo, s.p64x,
+    nn_wtree_kernel<<<grid, WT_WARPS * 32, 0, st>>>(t.wboxes, t.w, t.wpts, m.mhat, m.m64, m.geo, s.p64x,
                                                     s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm, s.idx,
                                                     use_prev, ctl, honor_done, progress);
 }
 
-// ICP_KD_GLOBAL_MIN (experiment): the CPU emulation gives horse 4.70 -> 3.79 leaves per search with the global levels
-// switched on below 131 072 points (tools/tree_order_emul.py); whether the costlier build pays is a GPU question.
-int kd_global_min_points()
-{
-    static const int v = [] {
-        const char* e = getenv("ICP_KD_GLOBAL_MIN");
-        const int x = e ? atoi(e) : 0;
-        return x >= 2 * KD_B ? x : KD_GLOBAL_MIN_POINTS;
-    }();
-    return v;
-}
+// Global k-d levels only from 131 072 model points up.  Round 2 measured them at 16 384 too (profiles/r02a_kdmin.md): the
+// resident loop gains 10 % (horse 2.79 -> 2.47 ms) but the costlier build loses 3-20 % end to end (horse_tr2 1.46 -> 1.79 ms),
+// and a drop-in is called one-shot; the switch was removed.
+int kd_global_min_points() { return KD_GLOBAL_MIN_POINTS; }
 
 size_t tree_sort_bytes(int n)
 {
@@ -703,7 +705,7 @@ void launch_nn_tree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int 
                     cudaStream_t st, int* progress)
 {
     const int grid = (int)((s.np + TREE_THREADS - 1) / TREE_THREADS);
-    nn_tree_kernel<<<grid, TREE_THREADS, 0, st>>>(t.nodes, t.pts, t.n_leaves, m.mhat, m.m64x, m.m64y, m.m64z, m.geo,
+    nn_tree_kernel<<<grid, TREE_THREADS, 0, st>>>(t.nodes, t.pts, t.n_leaves, m.mhat, m.m64, m.geo,
                                                   s.p64x, s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm,
                                                   s.idx, use_prev, ctl, honor_done, progress);
 }

@@ -230,7 +230,7 @@ class Context:
         return st.as_dict()
 
     def trace(self):
-        t = np.zeros(8)
+        t = np.zeros(10)
         _ck(self._L.icp_get_trace(self._h, _d(t)))
         return t
 

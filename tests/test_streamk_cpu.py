@@ -1,6 +1,6 @@
 """CPU model of the filter's work decomposition (csrc/nn_kernels.cu "stream-K", icp_api.cu choose_splits()).
 
-The np_pad/1024 scene tiles x nm_pad/64 model chunks form one linear sequence of T chunk-units; CTA b owns
+The np_pad/1536 scene tiles x nm_pad/128 model chunks form one linear sequence of T chunk-units; CTA b owns
 [b*T/n, (b+1)*T/n), writes one partial result per (CTA, scene tile) segment into slot = b - first CTA of that tile, and
 nn_refine_kernel recomputes the slot count of a tile from the same integers.  This restates that integer arithmetic
 and asserts, over small exhaustive sweeps and the sizes of BASELINE.json's configs, what the kernels rely on:
@@ -14,11 +14,10 @@ and asserts, over small exhaustive sweeps and the sizes of BASELINE.json's confi
 import numpy as np
 import pytest
 
-NN_TILE, NN_G, NN_TM = 1024, 64, 512
+NN_TILE, NN_G, NN_TM = 1536, 128, 512      # round 2 defaults: 12 scene points per thread, 128-point chunks
 CPM = NN_TM // NN_G
 SMS = 148
-MIN_CTAS = 4          # resident filter CTAs per SM (NN_MIN_CTAS)
-MIN_UNITS = 0         # ICP_NN_MIN_UNITS: least chunk-units per CTA (0 = one staged tile)
+MIN_CTAS = 3          # resident filter CTAs per SM (NN_MIN_CTAS)
 
 
 def pad(n, q):
@@ -34,10 +33,10 @@ def choose_splits(np_, nm, forced=0, sm_count=SMS):
     per_cta = 65536 // NN_G
     waves = max(1, (total + per_cta * wave - 1) // (per_cta * wave))
     n_cta = wave * waves
-    if forced > 0:
-        n_cta = forced
-    n_cta = min(n_cta, total // (MIN_UNITS if MIN_UNITS > 0 else CPM))
-    n_cta = max(n_cta, 1)
+    cap = max(total // CPM, min(total, sm_count))      # one staged tile per CTA, unless that leaves SMs without work
+    n_cta = max(min(n_cta, cap), 1)
+    if forced > 0:                                     # any grid up to one CTA per unit must work (the kernels are generic in it)
+        n_cta = min(forced, total)
     return n_cta, (n_cta + n_tiles - 1) // n_tiles + 1
 
 
@@ -96,7 +95,8 @@ def test_small_sweep_exhaustive():
                                     (262144, 262144), (6061, 48485), (131072, 1048576)])
 def test_config_sizes(np_, nm):
     n_cta, n_splits = check(np_, nm)
-    assert n_cta % (SMS * 4) == 0 or n_cta == (pad(np_, NN_TILE) // NN_TILE) * (pad(nm, NN_TM) // NN_G) // CPM
+    total = (pad(np_, NN_TILE) // NN_TILE) * (pad(nm, NN_TM) // NN_G)
+    assert n_cta % (SMS * MIN_CTAS) == 0 or n_cta == max(total // CPM, min(total, SMS))
     # whole waves, equal work: ranges differ by at most one chunk
     T = (pad(np_, NN_TILE) // NN_TILE) * (pad(nm, NN_TM) // NN_G)
     sizes = {(b + 1) * T // n_cta - b * T // n_cta for b in range(n_cta)}
@@ -104,14 +104,14 @@ def test_config_sizes(np_, nm):
 
 
 def test_largest_configuration_fits_the_kernel_state():
-    # 2^22 x 2^22 (BASELINE config 4): checked arithmetically, the full walk is 2.7e8 units
+    # 2^22 x 2^22 (BASELINE config 4): checked arithmetically, the full walk is 9e7 units
     np_ = nm = 1 << 22
     n_cta, n_splits = choose_splits(np_, nm)
-    n_tiles, cpt = np_ // NN_TILE, nm // NN_G
+    n_tiles, cpt = pad(np_, NN_TILE) // NN_TILE, nm // NN_G
     T = n_tiles * cpt
-    assert T == 4096 * 65536 and n_cta % (SMS * 4) == 0
+    assert (n_tiles, cpt) == (2731, 32768) and n_cta % (SMS * MIN_CTAS) == 0
     assert T // n_cta + 1 < 2 ** 31 and n_cta < 2 ** 31
-    assert 900 <= T / n_cta <= 1100                               # "~1 024-chunk ranges" of the design note
+    assert 450 <= T / n_cta <= 550                                # ranges of ~64 K model points x one scene tile
     assert n_splits * pad(np_, NN_TILE) * 4 < 2 ** 40             # scratch rows: a few hundred MB at most
     rng = np.random.default_rng(0)
     for b in list(rng.integers(0, n_cta, 200)) + [0, n_cta - 1]:
@@ -120,7 +120,7 @@ def test_largest_configuration_fits_the_kernel_state():
         assert all(0 <= s < n_splits for *_, s in segs)
 
 
-@pytest.mark.parametrize("r,g,ctas", [(8, 128, 4), (12, 64, 3), (12, 128, 3), (16, 64, 2)])
+@pytest.mark.parametrize("r,g,ctas", [(8, 64, 4), (8, 128, 4), (12, 64, 3), (12, 256, 3), (16, 128, 2)])
 def test_variant_geometries(monkeypatch, r, g, ctas):
     """The build-time variants of the filter (icp_common.cuh ICP_NN_R / _G / _MIN_CTAS, `make variants`) run the same
     integer arithmetic with other constants: 128-point chunks, 1 536- and 2 048-point scene tiles, 3 or 2 CTAs per SM."""
@@ -137,16 +137,15 @@ def test_variant_geometries(monkeypatch, r, g, ctas):
         check(5000, 4097, forced)
 
 
-@pytest.mark.parametrize("min_units", [1, 2, 4])
-def test_fine_decomposition_of_small_clouds(monkeypatch, min_units):
-    """ICP_NN_MIN_UNITS < 8: a CTA may own less than one staged model tile (cow: 144 chunk-units on up to 144 CTAs
-    instead of 18); ranges, slots and staged tiles must still be exactly what nn_refine expects."""
-    import sys
-    monkeypatch.setattr(sys.modules[__name__], "MIN_UNITS", min_units)
+def test_small_clouds_use_every_sm_they_can():
+    """A CTA normally owns at least one staged model tile, but never so few CTAs that SMs stay idle while chunk-units
+    remain (round 2: cow's filter 35 -> 25 us).  cow = 2 scene tiles x 24 chunks = 48 units -> 48 CTAs of one unit."""
+    n_cta, n_splits = check(2903, 2903)
+    assert n_cta == 48 and n_splits == 25
+    n_cta, _ = check(8192, 8192)                 # 6 tiles x 64 chunks = 384 units: one CTA per SM, not 96
+    assert n_cta == SMS
+    n_cta, _ = check(48485, 48485)               # horse: one full wave, ~27 chunks per CTA
+    assert n_cta == SMS * MIN_CTAS
     for np_ in (1, 1023, 1025, 2903, 5000, 9000):
         for nm in (1, 64, 65, 513, 2903, 4097):
-            n_cta, n_splits = check(np_, nm)
-            for forced in (1, 7, 37, 593, 5000):
-                check(np_, nm, forced)
-    n_cta, n_splits = check(2903, 2903)
-    assert n_cta == 144 // min_units and n_splits == (n_cta + 2) // 3 + 1
+            check(np_, nm)

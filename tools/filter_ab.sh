@@ -5,7 +5,7 @@
 # The default build runs first AND last so that drift of the box shows.   usage: bash tools/filter_ab.sh [variants...]
 cd "${GRAFT_REPO_ROOT:-.}"
 mkdir -p gpurun_out
-V="${@:-u4 u8 g128 g128u4 g128u8 g256u8 r12c3 r12c3u4 r12c3g128u4 r12c3g128u8 r16c2 r16c2g128u4 rf4 rf16 exseg2k exp8 exp2 red4 red3}"
+V="${@:-r8c4g64u2 r8c4g128u8 r12c3g256u8 r12c3g128u16 r16c2g128u8 r10c3g128u8 rf4 rf16 inp1 inp4}"
 LIBDIR=$PWD/iterative-closest-point_b200/lib
 run() {   # name, library
   export ICP_B200_LIB=$2
@@ -13,8 +13,6 @@ run() {   # name, library
   for w in horse syn256k; do
     timeout 300 python bench.py --skip-cpu-baseline --workload $w --steps 20 --warmup 3 > gpurun_out/ab_$1_$w.json 2> gpurun_out/ab_$1_$w.err
   done
-  # K2 / K4 as HBM-bound passes on 2^22 points (tree search so that the run takes milliseconds): the red* variants only
-  case $1 in red*|default_a) ICP_NN=tree timeout 300 python tools/prof_tail.py syn4m 3 > gpurun_out/ab_$1_tail.log 2>&1;; esac
 }
 run default_a $LIBDIR/libicp_b200.so
 for v in $V; do [ -f $LIBDIR/variants/libicp_b200_$v.so ] && run $v $LIBDIR/variants/libicp_b200_$v.so; done
@@ -34,4 +32,3 @@ for v in ["default_a"] + sys.argv[1:] + ["default_b"]:
         except Exception as e:
             print("%-14s %-8s failed: %s" % (v, w, e))
 PY
-grep -h "K2+K4" gpurun_out/ab_*_tail.log | tee -a gpurun_out/ab_summary.txt

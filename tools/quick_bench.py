@@ -35,24 +35,19 @@ def loop_timing(tag, m, p, max_iter=30, check=True):
     print(f"{tag}: loop {it} it  dev {st['ms_total']:.3f} ms (filter {st['ms_filter']:.3f} refine {st['ms_refine']:.3f} exact {st['ms_exact']:.3f} align {st['ms_align']:.3f} ms) wall {dt*1e3:.3f} ms  "
           f"{it/(st['ms_total']*1e-3):.1f} it/s  {it*len(m)*len(p)/(st['ms_total']*1e-3)/1e12:.3f} T evals/s  last err {hist[-1]:.3e}", flush=True)
     if os.environ.get("ICP_PROFILE"):
-        print("   align trace (us: gap after K1 | from entry: moments, partials, barrier, reduce, solve, transform, last block out):", np.round(ctx.trace(), 2))
+        print("   align trace (us: gap after K1 | from entry: moments, partials, barrier, reduce, solve, transform, last block out | partials re-read, block sum):", np.round(ctx.trace(), 2))
     ctx.close()
 
 if __name__ == "__main__":
     cow_r, cow_1 = load("cow_ref"), load("cow_tr1")
     closest_timing("cow", cow_r, cow_1); loop_timing("cow", cow_r, cow_1)
-    if os.environ.get("QB_ONLY_SMALL"):          # small clouds only (ICP_NN_MIN_UNITS experiment)
+    if os.environ.get("QB_ONLY_SMALL"):          # small clouds only
         for n in (8192, 16384):
             m, p, _ = synthetic_pair(n, seed=n)
             closest_timing(f"synthetic {n}", m, p); loop_timing(f"synthetic {n}", m, p, max_iter=10)
         sys.exit(0)
     h_r, h_1 = load("horse_ref"), load("horse_tr1")
     closest_timing("horse", h_r, h_1); loop_timing("horse_tr1", h_r, h_1)
-    for s in os.environ.get("QB_CTAS", "").split(","):
-        if s:
-            os.environ["ICP_NN_CTAS"] = s
-            closest_timing(f"horse ctas={s}", h_r, h_1)
-    os.environ.pop("ICP_NN_CTAS", None)
     for lg in (18, 20):
         m, p, _ = synthetic_pair(1 << lg, seed=lg)
         closest_timing(f"synthetic 2^{lg}", m, p, reps=3)
