@@ -170,6 +170,9 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
 int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
                   const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
                   int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out);
+/* Kernels of this library launched by the last icp_batch_run of the process (loop kernels as counted by icp_run + the
+ * preparation kernels of each pair; the radix sort of the scene is cub's and not counted). */
+long long icp_batch_kernels_launched(void);
 
 /* ---- multi-GPU (new; the reference is single-GPU) ----------------------------------------------
  * One context per GPU / rank holds a contiguous block of the scene and a replica of the model.

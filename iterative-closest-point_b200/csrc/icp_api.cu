@@ -1008,6 +1008,7 @@ int icp_y_p_norm_host(const double* y_xyz, const double* p_xyz, int64_t n, doubl
 // tail of an iteration (refine / exact / alignment) or copying over PCIe, the other lanes' filter
 // kernels keep the SMs busy.  Across GPUs the launcher deals pairs round-robin, one process per GPU.
 // Pool of idle lane contexts per device (icp_release_cached() empties it).
+static std::atomic<long long> g_batch_kernels{0};   // own kernels launched by the last icp_batch_run of this process
 static std::mutex g_pool_mu;
 static std::vector<std::pair<int, icp_ctx*>> g_pool;
 
@@ -1039,6 +1040,7 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     if ((int64_t)lanes > n_pairs) lanes = n_pairs > 0 ? (int)n_pairs : 1;
     std::atomic<int64_t> next{0};
     std::atomic<int> status{ICP_OK};
+    g_batch_kernels.store(0);
     std::mutex mu;
     std::string first_err;
     auto worker = [&]() {
@@ -1053,6 +1055,9 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
             if ((r = icp_set_model(c, m_xyz[k], nm[k])) || (r = icp_set_scene(c, p_xyz[k], np[k])) ||
                 (r = icp_run(c, max_iter, threshold, check_sizes, &it, hist.data())))
                 break;
+            // the loop's kernels (counted by icp_run) + the 7 preparation kernels of icp_set_model / icp_set_scene
+            // (2 x bbox, model_geo, model_build, scene_keys, scene_build; + scene_export below); cub's sort is not ours
+            g_batch_kernels.fetch_add(c->stats.kernels_launched + 6 + ((new_p_out && new_p_out[k]) ? 1 : 0));
             if (iters_out) iters_out[k] = it;
             if (err_out) err_out[k] = it > 0 ? hist[(size_t)it - 1] : 0.0;
             if (new_p_out && new_p_out[k] && (r = icp_get_scene(c, new_p_out[k]))) break;
@@ -1070,6 +1075,8 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     if (status.load() != ICP_OK) g_err = first_err;
     return status.load();
 }
+
+long long icp_batch_kernels_launched(void) { return g_batch_kernels.load(); }
 
 static void lane_pool_clear()
 {

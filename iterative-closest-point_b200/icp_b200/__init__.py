@@ -31,7 +31,7 @@ EXPORTS = [
     "icp_get_scene", "icp_reset_scene", "icp_closest", "icp_centroid", "icp_find_alignment", "icp_err_compute",
     "icp_get_transform", "icp_run", "icp_get_indices", "icp_get_stats", "icp_closest_matrix_host",
     "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
-    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run", "icp_release_cached",
+    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run", "icp_batch_kernels_launched", "icp_release_cached",
     "icp_set_nn_mode", "icp_get_nn_mode",
 ]
 
@@ -100,6 +100,7 @@ def load_library(path=None):
     L.icp_get_trace.argtypes = [vp, _dp]
     L.icp_batch_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
                                 C.POINTER(C.c_int64), C.c_int, C.c_double, C.c_int, _ip, _dp, C.c_void_p, _dp]
+    L.icp_batch_kernels_launched.restype = C.c_longlong
     L.icp_comm_peer_handle.argtypes = [vp, C.c_void_p]
     L.icp_comm_peer_attach.argtypes = [vp, C.c_void_p, C.c_int, C.c_int]
     _lib = L
@@ -273,7 +274,7 @@ def batch_run(models, scenes, max_iter=30, threshold=1e-5, check_sizes=True, dev
     op = PP(*[_d(a) for a in outs]) if want_scene else None
     _ck(L.icp_batch_run(int(device), int(lanes), n, mp, nm, pp, npts, int(max_iter), float(threshold),
                         int(bool(check_sizes)), _i(iters), _d(err), op, _d(srt)))
-    res = dict(iters=iters[:n], err=err[:n], srt=srt[:n])
+    res = dict(iters=iters[:n], err=err[:n], srt=srt[:n], kernels_launched=int(L.icp_batch_kernels_launched()))
     if want_scene:
         res["new_p"] = outs
     return res
