@@ -193,6 +193,39 @@ int icp_comm_world(icp_ctx* ctx, int* rank, int* world);
 int icp_comm_peer_handle(icp_ctx* ctx, void* handle64);
 int icp_comm_peer_attach(icp_ctx* ctx, const void* handles /* world x 64 bytes, rank order */, int rank, int world);
 
+/* ---- one process, several GPUs: the multi-device form of icp_create (icp_create(ctx, devices, ndev)) ----
+ * An icp_group owns one context per listed device.  icp_group_set_model replicates the model, icp_group_set_scene cuts
+ * the scene into `ndev` contiguous blocks (device i holds block i); icp_group_run is find_corresponding
+ * (src/cpu.cc:55-79) over the sharded scene: per iteration the 18 moment sums and the residual are exchanged INSIDE the
+ * alignment kernels through mailboxes in peer memory (cudaDeviceEnablePeerAccess over NVLink; no NCCL, no launcher, no
+ * torch), every device solves for the identical (s, R, t), and results come back in the caller's point order.  Indices,
+ * iteration count and error values are those of the single-device loop.  Devices must be distinct and peer-accessible
+ * (ICP_ERR_COMM otherwise); with one device the group is a plain context.  The calls below are collective over the
+ * group's devices (each device is driven by its own host thread for the duration of the call) and otherwise mirror
+ * their icp_* namesakes.  icp_group_member gives the per-device context (for icp_get_stats / icp_get_trace only). */
+typedef struct icp_group icp_group;
+int icp_group_create(icp_group** grp, const int* devices, int ndev);
+void icp_group_destroy(icp_group* grp);
+int icp_group_size(icp_group* grp);
+icp_ctx* icp_group_member(icp_group* grp, int i);
+int icp_group_set_model(icp_group* grp, const double* m_xyz, int64_t nm);
+int icp_group_set_scene(icp_group* grp, const double* p_xyz, int64_t np);
+int icp_group_reset_scene(icp_group* grp);
+int icp_group_set_nn_mode(icp_group* grp, int mode);
+int icp_group_closest(icp_group* grp, int32_t* idx_out, double* Y_out);
+int icp_group_centroid(icp_group* grp, double mu_p[3], double mu_y[3]);
+int icp_group_find_alignment(icp_group* grp, double* s, double R[9], double t[3], double* err_align);
+int icp_group_err_compute(icp_group* grp, int in_place, double* err);
+int icp_group_run(icp_group* grp, int max_iter, double threshold, int check_sizes, int* iters_done, double* err_hist);
+int icp_group_get_scene(icp_group* grp, double* p_xyz_out);
+int icp_group_get_indices(icp_group* grp, int32_t* idx_out);
+int icp_group_get_transform(icp_group* grp, double* s, double R[9], double t[3]);
+int icp_group_get_stats(icp_group* grp, icp_stats* out);   /* sizes, pairs, launches summed; times of the slowest device */
+/* icp_batch_run over several devices of this process: pair k is registered on device k % ndev, `lanes` contexts per device. */
+int icp_batch_run_multi(const int* devices, int ndev, int lanes, int64_t n_pairs, const double* const* m_xyz,
+                        const int64_t* nm, const double* const* p_xyz, const int64_t* np, int max_iter, double threshold,
+                        int check_sizes, int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out);
+
 #ifdef __cplusplus
 }
 #endif

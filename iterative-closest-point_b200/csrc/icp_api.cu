@@ -117,6 +117,8 @@ struct icp_ctx {
     PeerMailbox* d_mailbox = nullptr;
     PeerComm peer;
     bool peer_ready = false, force_nccl = false;
+    bool in_group = false;                 // member of an icp_group (one process, several devices): mailboxes reached by peer access
+    double group_np = 0.0;                 // global scene size of the group (what alignement_check compares)
     int align_mode = 0;                    // 0 auto, 1 fused, 2 split (ICP_ALIGN)
     bool is_lane = false;                  // a context of icp_batch_run: shares the GPU with other lanes
     unsigned long long* d_trace = nullptr; // ICP_PROFILE=1: phase time stamps of the last fused alignment kernel
@@ -307,6 +309,8 @@ void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent
 // ICP_ALIGN=fused|split forces one; the default picks per context (see align_step).
 // A communicator without mailboxes (or ICP_COMM=nccl) takes the NCCL path: separate kernels + ncclAllReduce.
 bool nccl_path(const icp_ctx* c) { return c->comm && (!c->peer_ready || c->force_nccl); }
+// the in-kernel exchange: peer mailboxes attached (CUDA IPC between processes, or peer access inside an icp_group)
+const PeerComm* peers_of(const icp_ctx* c) { return (c->peer_ready && !nccl_path(c) && (c->comm || c->in_group)) ? &c->peer : nullptr; }
 
 int fused_blocks(const icp_ctx* c)
 {
@@ -345,13 +349,13 @@ int wait_progress(icp_ctx* c, int need, int enqueued)
 // Returns the number of kernels launched (> 0) or a negative icp_status.
 int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_global, double threshold)
 {
-    const PeerComm* peers = (c->comm && c->peer_ready) ? &c->peer : nullptr;
+    const PeerComm* peers = peers_of(c);
     int launched;
     // auto: the cooperative kernel where it was measured faster (one GPU, nothing else on it: 11.17 vs 11.27 ms per
     // horse loop), the split pair with peers (its second grid barrier costs more than a launch: 11.65 vs 11.61 ms
     // at N = 2) and in batch lanes (no co-residency requirement between concurrent contexts).
     // Large scenes take the split pair as well: no co-residency limit on the grid (2^22 points: 225 vs 245 us).
-    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->is_lane && c->s.np <= 262144);
+    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->in_group && !c->is_lane && c->s.np <= 262144);
     if (fused) {
         const int e = launch_align_fused(c->m, c->s, c->d_partials, fused_blocks(c), c->d_mom, c->d_xf, c->d_err_sum,
                                          c->d_ctl, honor_done, in_place, finish, n_global, threshold, c->d_err_hist, peers,
@@ -460,7 +464,7 @@ void icp_destroy(icp_ctx* c)
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (int r = 0; r < c->peer.world; ++r)
-        if (c->peer_ready && r != c->peer.rank && c->peer.box[r]) cudaIpcCloseMemHandle(c->peer.box[r]);
+        if (c->peer_ready && !c->in_group && r != c->peer.rank && c->peer.box[r]) cudaIpcCloseMemHandle(c->peer.box[r]);
     dfree(c->d_mailbox); dfree(c->d_trace);
     if (c->h_progress) cudaFreeHost(c->h_progress);
     dfree(c->m.m64); dfree(c->m.mhat); dfree(c->m.geo);
@@ -668,8 +672,8 @@ int icp_centroid(icp_ctx* c, double mu_p[3], double mu_y[3])
     int r;
     if ((r = need_idx(c, "icp_centroid"))) return r;
     CK(cudaSetDevice(c->device));
-    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, nullptr, c->st);
-    if ((r = allreduce(c, c->d_mom, MOM_N))) return r;
+    launch_moments(c->m, c->s, c->d_partials, c->n_red_blocks, c->d_mom, c->d_ctl, 0, nullptr, c->st, peers_of(c));
+    if (!peers_of(c) && (r = allreduce(c, c->d_mom, MOM_N))) return r;
     launch_centroid_export(c->m, c->d_mom, c->d_out6, c->st);
     double h[6];
     CK(cudaMemcpyAsync(h, c->d_out6, sizeof(h), cudaMemcpyDeviceToHost, c->st));
@@ -723,8 +727,8 @@ int icp_err_compute(icp_ctx* c, int in_place, double* err)
     if ((r = need_idx(c, "icp_err_compute"))) return r;
     CK(cudaSetDevice(c->device));
     launch_transform(c->m, c->s, c->d_xf, in_place ? 1 : 0, c->d_partials, c->n_red_blocks, c->d_err_sum, c->d_ctl, 0,
-                     0, 1.0, 0.0, nullptr, c->st);
-    if ((r = allreduce(c, c->d_err_sum, 1))) return r;
+                     0, 1.0, 0.0, nullptr, c->st, peers_of(c));
+    if (!peers_of(c) && (r = allreduce(c, c->d_err_sum, 1))) return r;
     CK(cudaGetLastError());
     double e;
     CK(cudaMemcpyAsync(&e, c->d_err_sum, sizeof(e), cudaMemcpyDeviceToHost, c->st));
@@ -741,6 +745,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     int r;
     // alignement_check, src/cpu.cc:42-53 (with a communicator the GLOBAL scene size is what counts)
     double np_glob = (double)c->s.np;
+    if (c->in_group) np_glob = c->group_np;
     if (c->comm) {
         CK(cudaMemcpyAsync(c->d_err_sum, &np_glob, sizeof(double), cudaMemcpyHostToDevice, c->st));
         if ((r = allreduce(c, c->d_err_sum, 1))) return r;
@@ -1030,9 +1035,10 @@ static void lane_pool_give(int device, icp_ctx* c)
     g_pool.emplace_back(device, c);
 }
 
-int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
-                  const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
-                  int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out)
+static int icp_batch_run_device(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
+                                const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
+                                int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out,
+                                long long* launched_out)
 {
     if (n_pairs < 0 || (n_pairs > 0 && (!m_xyz || !nm || !p_xyz || !np))) { g_err = "icp_batch_run: bad arguments"; return ICP_ERR_INVALID; }
     if (lanes < 1) lanes = 1;
@@ -1040,7 +1046,7 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     if ((int64_t)lanes > n_pairs) lanes = n_pairs > 0 ? (int)n_pairs : 1;
     std::atomic<int64_t> next{0};
     std::atomic<int> status{ICP_OK};
-    g_batch_kernels.store(0);
+    std::atomic<long long> launched{0};
     std::mutex mu;
     std::string first_err;
     auto worker = [&]() {
@@ -1057,7 +1063,7 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
                 break;
             // the loop's kernels (counted by icp_run) + the 7 preparation kernels of icp_set_model / icp_set_scene
             // (2 x bbox, model_geo, model_build, scene_keys, scene_build; + scene_export below); cub's sort is not ours
-            g_batch_kernels.fetch_add(c->stats.kernels_launched + 6 + ((new_p_out && new_p_out[k]) ? 1 : 0));
+            launched.fetch_add(c->stats.kernels_launched + 6 + ((new_p_out && new_p_out[k]) ? 1 : 0));
             if (iters_out) iters_out[k] = it;
             if (err_out) err_out[k] = it > 0 ? hist[(size_t)it - 1] : 0.0;
             if (new_p_out && new_p_out[k] && (r = icp_get_scene(c, new_p_out[k]))) break;
@@ -1073,8 +1079,21 @@ int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m
     for (int i = 0; i < lanes; ++i) th.emplace_back(worker);
     for (auto& t : th) t.join();
     if (status.load() != ICP_OK) g_err = first_err;
+    if (launched_out) *launched_out = launched.load();
     return status.load();
 }
+
+int icp_batch_run(int device, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
+                  const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
+                  int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out)
+{
+    long long launched = 0;
+    const int r = icp_batch_run_device(device, lanes, n_pairs, m_xyz, nm, p_xyz, np, max_iter, threshold, check_sizes, iters_out,
+                                       err_out, new_p_out, srt_out, &launched);
+    g_batch_kernels.store(launched);
+    return r;
+}
+
 
 long long icp_batch_kernels_launched(void) { return g_batch_kernels.load(); }
 
@@ -1160,6 +1179,273 @@ int icp_comm_world(icp_ctx* c, int* rank, int* world)
     if (!c) return ICP_ERR_INVALID;
     if (rank) *rank = c->rank;
     if (world) *world = c->world;
+    return ICP_OK;
+}
+
+
+// ---- one process, several devices (icp_create(ctx, devices, ndev)) --------------------------------
+// An icp_group owns one context per device.  The model is replicated, the scene is cut into contiguous blocks (member
+// i holds block i), and the per-iteration exchange is the same in-kernel mailbox protocol the multi-process path uses —
+// the mailboxes are simply reached through peer access (cudaDeviceEnablePeerAccess) instead of CUDA IPC; no NCCL, no
+// launcher.  Every collective call runs its members concurrently on one host thread each (icp_run keeps its own
+// look-ahead loop per device).  Loop being sharded: src/cpu.cc:55-79.
+
+}  // extern "C" (the group's internals are C++)
+
+struct icp_group {
+    std::vector<icp_ctx*> ctx;
+    std::vector<int64_t> lo;          // member i holds scene points [lo[i], lo[i+1])
+    int64_t np = 0;
+};
+
+namespace {
+
+// Runs f(i, member i) for every member concurrently; returns the first failing status (its message in g_err).
+template <class F>
+int group_parallel(icp_group* g, F f)
+{
+    const int n = (int)g->ctx.size();
+    if (n == 1) return f(0, g->ctx[0]);
+    std::vector<int> rc((size_t)n, ICP_OK);
+    std::vector<std::string> msg((size_t)n);
+    std::vector<std::thread> th;
+    for (int i = 0; i < n; ++i)
+        th.emplace_back([&, i]() {
+            rc[(size_t)i] = f(i, g->ctx[(size_t)i]);
+            if (rc[(size_t)i]) msg[(size_t)i] = g_err;       // g_err is thread-local
+        });
+    for (auto& t : th) t.join();
+    for (int i = 0; i < n; ++i)
+        if (rc[(size_t)i]) { g_err = "device " + std::to_string(g->ctx[(size_t)i]->device) + ": " + msg[(size_t)i]; return rc[(size_t)i]; }
+    return ICP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int icp_group_create(icp_group** out, const int* devices, int ndev)
+{
+    if (!out || !devices || ndev < 1 || ndev > PEER_MAX_WORLD) { g_err = "icp_group_create: bad arguments (1..16 devices)"; return ICP_ERR_INVALID; }
+    *out = nullptr;
+    for (int i = 0; i < ndev; ++i)
+        for (int j = 0; j < i; ++j)
+            if (devices[i] == devices[j]) { g_err = "icp_group_create: a device is listed twice"; return ICP_ERR_INVALID; }
+    icp_group* g = new icp_group();
+    int r = ICP_OK;
+    for (int i = 0; i < ndev && !r; ++i) {
+        icp_ctx* c = nullptr;
+        r = icp_create(&c, devices[i]);
+        if (!r) g->ctx.push_back(c);
+    }
+    if (!r && ndev > 1) {
+        for (int i = 0; i < ndev && !r; ++i) {
+            icp_ctx* c = g->ctx[(size_t)i];
+            if (cudaSetDevice(c->device) != cudaSuccess) { g_err = "icp_group_create: cudaSetDevice failed"; r = ICP_ERR_CUDA; break; }
+            for (int j = 0; j < ndev && !r; ++j) {
+                if (j == i) continue;
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, c->device, devices[j]);
+                if (!can) { g_err = "icp_group_create: device " + std::to_string(c->device) + " cannot access device " + std::to_string(devices[j]) + " (no peer path)"; r = ICP_ERR_COMM; break; }
+                const cudaError_t e = cudaDeviceEnablePeerAccess(devices[j], 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { g_err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e); r = ICP_ERR_CUDA; break; }
+                cudaGetLastError();
+            }
+            if (r) break;
+            if (cudaMalloc((void**)&c->d_mailbox, sizeof(PeerMailbox)) != cudaSuccess ||
+                cudaMemset(c->d_mailbox, 0, sizeof(PeerMailbox)) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+                g_err = "icp_group_create: mailbox allocation failed";
+                r = ICP_ERR_CUDA;
+            }
+        }
+        for (int i = 0; i < ndev && !r; ++i) {
+            icp_ctx* c = g->ctx[(size_t)i];
+            for (int k = 0; k < PEER_MAX_WORLD; ++k) c->peer.box[k] = k < ndev ? g->ctx[(size_t)k]->d_mailbox : nullptr;
+            c->peer.rank = i;
+            c->peer.world = ndev;
+            c->rank = i;
+            c->world = ndev;
+            c->peer_ready = true;
+            c->in_group = true;
+        }
+    }
+    if (r) {
+        const std::string why = g_err;
+        icp_group_destroy(g);
+        g_err = why;
+        return r;
+    }
+    g->lo.assign((size_t)ndev + 1, 0);
+    *out = g;
+    return ICP_OK;
+}
+
+void icp_group_destroy(icp_group* g)
+{
+    if (!g) return;
+    for (icp_ctx* c : g->ctx) icp_destroy(c);
+    delete g;
+}
+
+int icp_group_size(icp_group* g) { return g ? (int)g->ctx.size() : 0; }
+icp_ctx* icp_group_member(icp_group* g, int i) { return (g && i >= 0 && i < (int)g->ctx.size()) ? g->ctx[(size_t)i] : nullptr; }
+
+int icp_group_set_model(icp_group* g, const double* m_xyz, int64_t nm)
+{
+    if (!g) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int, icp_ctx* c) { return icp_set_model(c, m_xyz, nm); });
+}
+
+int icp_group_set_scene(icp_group* g, const double* p_xyz, int64_t np)
+{
+    const int n = g ? (int)g->ctx.size() : 0;
+    if (!g || !p_xyz || np < n) { g_err = "icp_group_set_scene: bad arguments (at least one scene point per device)"; return ICP_ERR_INVALID; }
+    const int64_t base = np / n, rem = np % n;
+    for (int i = 0; i <= n; ++i) g->lo[(size_t)i] = i * base + (i < rem ? i : rem);
+    g->np = np;
+    return group_parallel(g, [&](int i, icp_ctx* c) {
+        c->group_np = (double)np;
+        return icp_set_scene(c, p_xyz + 3 * g->lo[(size_t)i], g->lo[(size_t)i + 1] - g->lo[(size_t)i]);
+    });
+}
+
+int icp_group_reset_scene(icp_group* g)
+{
+    if (!g) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int, icp_ctx* c) { return icp_reset_scene(c); });
+}
+
+int icp_group_set_nn_mode(icp_group* g, int mode)
+{
+    if (!g) return ICP_ERR_INVALID;
+    for (icp_ctx* c : g->ctx) { const int r = icp_set_nn_mode(c, mode); if (r) return r; }
+    return ICP_OK;
+}
+
+int icp_group_closest(icp_group* g, int32_t* idx_out, double* Y_out)
+{
+    if (!g) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int i, icp_ctx* c) {
+        return icp_closest(c, idx_out ? idx_out + g->lo[(size_t)i] : nullptr, Y_out ? Y_out + 3 * g->lo[(size_t)i] : nullptr);
+    });
+}
+
+int icp_group_run(icp_group* g, int max_iter, double threshold, int check_sizes, int* iters_done, double* err_hist)
+{
+    if (!g) return ICP_ERR_INVALID;
+    const int n = (int)g->ctx.size();
+    std::vector<int> it((size_t)n, 0);
+    const int r = group_parallel(g, [&](int i, icp_ctx* c) {
+        return icp_run(c, max_iter, threshold, check_sizes, &it[(size_t)i], i == 0 ? err_hist : nullptr);
+    });
+    if (r) return r;
+    for (int i = 1; i < n; ++i)
+        if (it[(size_t)i] != it[0]) { g_err = "icp_group_run: the devices disagree on the iteration count"; return ICP_ERR_COMM; }
+    if (iters_done) *iters_done = it[0];
+    return ICP_OK;
+}
+
+int icp_group_find_alignment(icp_group* g, double* s, double R[9], double t[3], double* err_align)
+{
+    if (!g) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int i, icp_ctx* c) {
+        return i == 0 ? icp_find_alignment(c, s, R, t, err_align) : icp_find_alignment(c, nullptr, nullptr, nullptr, nullptr);
+    });
+}
+
+int icp_group_err_compute(icp_group* g, int in_place, double* err)
+{
+    if (!g) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int i, icp_ctx* c) { return icp_err_compute(c, in_place, i == 0 ? err : nullptr); });
+}
+
+int icp_group_centroid(icp_group* g, double mu_p[3], double mu_y[3])
+{
+    if (!g) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int i, icp_ctx* c) { return icp_centroid(c, i == 0 ? mu_p : nullptr, i == 0 ? mu_y : nullptr); });
+}
+
+int icp_group_get_scene(icp_group* g, double* p_xyz_out)
+{
+    if (!g || !p_xyz_out) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int i, icp_ctx* c) { return icp_get_scene(c, p_xyz_out + 3 * g->lo[(size_t)i]); });
+}
+
+int icp_group_get_indices(icp_group* g, int32_t* idx_out)
+{
+    if (!g || !idx_out) return ICP_ERR_INVALID;
+    return group_parallel(g, [&](int i, icp_ctx* c) { return icp_get_indices(c, idx_out + g->lo[(size_t)i]); });
+}
+
+int icp_group_get_transform(icp_group* g, double* s, double R[9], double t[3])
+{
+    if (!g) return ICP_ERR_INVALID;
+    return icp_get_transform(g->ctx[0], s, R, t);
+}
+
+// Whole-group view: sizes and pair counts summed, times = the slowest device, launches summed.
+int icp_group_get_stats(icp_group* g, icp_stats* out)
+{
+    if (!g || !out) return ICP_ERR_INVALID;
+    icp_stats a{};
+    for (size_t i = 0; i < g->ctx.size(); ++i) {
+        icp_stats s1;
+        icp_get_stats(g->ctx[i], &s1);
+        if (i == 0) a = s1;
+        else {
+            a.np += s1.np; a.nn_pairs += s1.nn_pairs; a.rerank_full += s1.rerank_full; a.rerank_chunk += s1.rerank_chunk;
+            a.kernels_launched += s1.kernels_launched;
+            a.ms_filter = s1.ms_filter > a.ms_filter ? s1.ms_filter : a.ms_filter;
+            a.ms_total = s1.ms_total > a.ms_total ? s1.ms_total : a.ms_total;
+        }
+    }
+    *out = a;
+    return ICP_OK;
+}
+
+// icp_batch_run over several devices: `lanes` contexts per device, all pulling pairs from one shared counter.
+int icp_batch_run_multi(const int* devices, int ndev, int lanes, int64_t n_pairs, const double* const* m_xyz, const int64_t* nm,
+                        const double* const* p_xyz, const int64_t* np, int max_iter, double threshold, int check_sizes,
+                        int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out)
+{
+    if (!devices || ndev < 1) { g_err = "icp_batch_run_multi: bad arguments"; return ICP_ERR_INVALID; }
+    if (ndev == 1)
+        return icp_batch_run(devices[0], lanes, n_pairs, m_xyz, nm, p_xyz, np, max_iter, threshold, check_sizes, iters_out,
+                             err_out, new_p_out, srt_out);
+    // pair k goes to device k % ndev (any deal is correct: pairs are independent); the devices run concurrently
+    std::vector<int> rc((size_t)ndev, ICP_OK);
+    std::vector<std::string> msg((size_t)ndev);
+    std::vector<long long> launched((size_t)ndev, 0);
+    std::vector<std::thread> th;
+    for (int d = 0; d < ndev; ++d)
+        th.emplace_back([&, d]() {
+            std::vector<const double*> mm, pp;
+            std::vector<double*> oo;
+            std::vector<int64_t> nmm, npp, ids;
+            for (int64_t k = d; k < n_pairs; k += ndev) {
+                ids.push_back(k); mm.push_back(m_xyz[k]); pp.push_back(p_xyz[k]); nmm.push_back(nm[k]); npp.push_back(np[k]);
+                oo.push_back(new_p_out ? new_p_out[k] : nullptr);
+            }
+            const int64_t n = (int64_t)ids.size();
+            std::vector<int32_t> it((size_t)(n ? n : 1));
+            std::vector<double> er((size_t)(n ? n : 1)), srt((size_t)(n ? n : 1) * 13);
+            rc[(size_t)d] = icp_batch_run_device(devices[d], lanes, n, mm.data(), nmm.data(), pp.data(), npp.data(), max_iter, threshold,
+                                                 check_sizes, it.data(), er.data(), new_p_out ? oo.data() : nullptr, srt.data(),
+                                                 &launched[(size_t)d]);
+            if (rc[(size_t)d]) msg[(size_t)d] = g_err;
+            for (int64_t j = 0; j < n && !rc[(size_t)d]; ++j) {
+                if (iters_out) iters_out[ids[(size_t)j]] = it[(size_t)j];
+                if (err_out) err_out[ids[(size_t)j]] = er[(size_t)j];
+                if (srt_out) memcpy(srt_out + 13 * ids[(size_t)j], srt.data() + 13 * j, 13 * sizeof(double));
+            }
+        });
+    for (auto& t : th) t.join();
+    long long total = 0;
+    for (int d = 0; d < ndev; ++d) {
+        if (rc[(size_t)d]) { g_err = "device " + std::to_string(devices[d]) + ": " + msg[(size_t)d]; return rc[(size_t)d]; }
+        total += launched[(size_t)d];
+    }
+    g_batch_kernels.store(total);
     return ICP_OK;
 }
 

@@ -6,7 +6,10 @@
 //   one-shot   through the reference-shaped stateless entry point (host matrices in, host results out: context
 //              creation, uploads, Morton sort, kernels, downloads — what BM_GPU_* measures in the reference)
 //   resident   on a context that already holds the clouds (kernels + result read-back only)
-// Usage: bench [ref.txt scene.txt] [--json]      (defaults: the reference's REF_PATH / SCENE_PATH)
+// Usage: bench [ref.txt scene.txt] [--json] [--devices 0,1,...]     (defaults: the reference's REF_PATH / SCENE_PATH)
+//   --devices  adds the resident loop over several GPUs of this process (icp_group_*: the scene cut into contiguous
+//              blocks, strong scaling) next to the single-GPU lines; ICP_DEVICES in the environment moves the ICP objects
+//              of the one-shot lines too (host/icp.hh).
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
@@ -53,9 +56,18 @@ int main(int argc, char* argv[])
     const char* scene_path = "data_students/cow_tr1.txt";
     bool json = false;
     std::vector<const char*> pos;
+    std::vector<int> devices;
     for (int i = 1; i < argc; ++i) {
         if (!std::strcmp(argv[i], "--json")) json = true;
-        else pos.push_back(argv[i]);
+        else if (!std::strcmp(argv[i], "--devices") && i + 1 < argc) {
+            for (const char* q = argv[++i]; *q;) {
+                char* end = nullptr;
+                const long v = std::strtol(q, &end, 10);
+                if (end == q) break;
+                devices.push_back((int)v);
+                q = (*end == ',') ? end + 1 : end;
+            }
+        } else pos.push_back(argv[i]);
     }
     if (pos.size() >= 2) { ref_path = pos[0]; scene_path = pos[1]; }
     const int loop_iters = 20;                                      // src/bench.cc:385,435-445
@@ -114,6 +126,23 @@ int main(int argc, char* argv[])
     CHECK(icp_get_stats(ctx, &st));
     icp_destroy(ctx);
 
+    // ---- the same resident loop over several GPUs of this process -------------------------------------
+    icp_stats gst{};
+    int giters = 0;
+    if (devices.size() > 1) {
+        icp_group* grp = nullptr;
+        CHECK(icp_group_create(&grp, devices.data(), (int)devices.size()));
+        CHECK(icp_group_set_model(grp, m.data(), nm));
+        CHECK(icp_group_set_scene(grp, p.data(), np));
+        out.push_back(measure("resident_loop_group", "icp_group_reset_scene + icp_group_run(max_iter 20) on " + std::to_string(devices.size()) + " GPUs (a9, scene sharded)", [&] {
+            CHECK(icp_group_reset_scene(grp));
+            CHECK(icp_group_run(grp, loop_iters, 1e-5, 0, &giters, hist.data()));
+        }));
+        CHECK(icp_group_get_stats(grp, &gst));
+        icp_group_destroy(grp);
+        if (giters != iters) { std::fprintf(stderr, "[bench] the group loop ran %d iterations, the single-GPU loop %d\n", giters, iters); return 4; }
+    }
+
     if (json) {
         std::printf("{\"ref\": \"%s\", \"scene\": \"%s\", \"np\": %ld, \"nm\": %ld, \"loop_iterations\": %d, \"benchmarks\": [", ref_path,
                     scene_path, np, nm, iters);
@@ -124,6 +153,9 @@ int main(int argc, char* argv[])
     } else {
         std::printf("%s vs %s: np = %ld, nm = %ld; loops stop after %d iterations; device loop %.3f ms\n", ref_path, scene_path, np, nm,
                     iters, st.ms_total);
+        if (devices.size() > 1)
+            std::printf("group of %zu GPUs: %d iterations, device loop %.3f ms (slowest device), filter %.3f ms\n", devices.size(), giters,
+                        gst.ms_total, gst.ms_filter);
         std::printf("%-34s %12s %12s %6s %12s   %s\n", "Benchmark", "Time (ms)", "min (ms)", "reps", "frame_rate", "reference capture");
         for (const auto& r : out)
             std::printf("%-34s %12.4f %12.4f %6d %12.2f   %s\n", r.name.c_str(), r.mean_ms, r.min_ms, r.reps, 1000.0 / r.mean_ms,

@@ -105,6 +105,24 @@ inline void release_ctx(icp_ctx* c)
     else icp_destroy(c);
 }
 
+// ICP_DEVICES=0,1,...  (environment): ICP objects run their loop on those GPUs of this process — the scene cut into
+// contiguous blocks, the model replicated, the exchange inside the alignment kernels over peer memory (icp_group_*,
+// include/icp_b200.h).  Unset or a single device: one GPU, as before.  Results do not depend on it.
+inline std::vector<int> env_devices()
+{
+    std::vector<int> d;
+    if (const char* e = std::getenv("ICP_DEVICES")) {
+        for (const char* q = e; *q;) {
+            char* end = nullptr;
+            const long v = std::strtol(q, &end, 10);
+            if (end == q) break;
+            d.push_back((int)v);
+            q = (*end == ',') ? end + 1 : end;
+        }
+    }
+    return d;
+}
+
 // row-major double[9] <-> column-major 3x3 Matrix
 inline void to_rowmajor3(const Matrix& m, double out[9])
 {
@@ -190,10 +208,7 @@ public:
         s = 1.;
         r = Matrix::Identity(3, 3);
         t = Matrix::Zero(3, 1);
-        int rc = acquire_ctx(&ctx);
-        if (rc) die("icp_create", rc);
-        if ((rc = icp_set_model(ctx, m.data(), nm))) die("icp_set_model", rc);
-        if ((rc = icp_set_scene(ctx, new_p.data(), np))) die("icp_set_scene", rc);
+        ensure_ctx();
     }
     // The reference's ICP objects are plain host values and its harness copies them freely (src/bench.cc:186-189,
     // 211-226, 362-381).  A copy takes the host state (m, p, new_p, s, r, t); its device context is created on
@@ -204,7 +219,11 @@ public:
     {
     }
     ICP& operator=(const ICP&) = delete;
-    ~ICP() { release_ctx(ctx); }
+    ~ICP()
+    {
+        release_ctx(ctx);
+        if (grp) icp_group_destroy(grp);
+    }
 
     closest_matrix_params get_closest_matrix_params() { return {dim, np, nm, new_p, m}; }
     err_compute_params get_err_compute_params(Matrix& Y) { return {np, new_p, s, r, t, Y}; }
@@ -241,14 +260,15 @@ public:
         if (check_sizes) alignement_check();
         ensure_ctx();
         std::vector<double> hist((size_t)(max_iter > 0 ? max_iter : 1));
-        int rc = icp_run(ctx, max_iter, threshold, 0, &iterations, hist.data());
+        int rc = grp ? icp_group_run(grp, max_iter, threshold, 0, &iterations, hist.data())
+                     : icp_run(ctx, max_iter, threshold, 0, &iterations, hist.data());
         if (rc) die("icp_run", rc);
         for (int i = 0; i < iterations; i++) {
             std::cerr << "[ICP] iteration number " << i << " | ";
             std::cerr << "error value = " << hist[(size_t)i] << std::endl;
         }
         errors.assign(hist.begin(), hist.begin() + iterations);
-        if ((rc = icp_get_scene(ctx, new_p.data()))) die("icp_get_scene", rc);
+        if ((rc = grp ? icp_group_get_scene(grp, new_p.data()) : icp_get_scene(ctx, new_p.data()))) die("icp_get_scene", rc);
         pull_transform();
     }
     void find_corresponding_opti() { find_corresponding(); }    // src/GPU/gpu.cc:52-83
@@ -258,7 +278,7 @@ public:
     {
         Matrix Y(dim, np);
         ensure_ctx();
-        int rc = icp_closest(ctx, nullptr, Y.data());
+        int rc = grp ? icp_group_closest(grp, nullptr, Y.data()) : icp_closest(ctx, nullptr, Y.data());
         if (rc) die("icp_closest", rc);
         return Y;
     }
@@ -277,7 +297,8 @@ public:
     double scale() const { return s; }
     const Matrix& rotation() const { return r; }
     const Matrix& translation() const { return t; }
-    icp_ctx* handle() { ensure_ctx(); return ctx; }
+    icp_ctx* handle() { ensure_ctx(); return grp ? icp_group_member(grp, 0) : ctx; }
+    icp_group* group() { ensure_ctx(); return grp; }
 
 public:
     Matrix new_p;
@@ -285,10 +306,19 @@ public:
     std::vector<double> errors;
 
 private:
-    void ensure_ctx()     // copies only: a constructed object already owns its context
+    void ensure_ctx()     // the constructor, and copies on first use
     {
-        if (ctx) return;
-        int rc = acquire_ctx(&ctx);
+        if (ctx || grp) return;
+        const std::vector<int> devs = env_devices();
+        int rc;
+        if (devs.size() > 1 && np >= devs.size()) {
+            if ((rc = icp_group_create(&grp, devs.data(), (int)devs.size()))) die("icp_group_create", rc);
+            if ((rc = icp_group_set_model(grp, m.data(), nm))) die("icp_group_set_model", rc);
+            if ((rc = icp_group_set_scene(grp, new_p.data(), np))) die("icp_group_set_scene", rc);
+            return;
+        }
+        if (devs.size() == 1) rc = icp_create(&ctx, devs[0]);
+        else rc = acquire_ctx(&ctx);
         if (rc) die("icp_create", rc);
         if ((rc = icp_set_model(ctx, m.data(), nm))) die("icp_set_model", rc);
         if ((rc = icp_set_scene(ctx, new_p.data(), np))) die("icp_set_scene", rc);
@@ -296,7 +326,7 @@ private:
     void pull_transform()
     {
         double R_[9], t_[3];
-        int rc = icp_get_transform(ctx, &s, R_, t_);
+        int rc = grp ? icp_group_get_transform(grp, &s, R_, t_) : icp_get_transform(ctx, &s, R_, t_);
         if (rc) die("icp_get_transform", rc);
         r = from_rowmajor3(R_);
         for (int i = 0; i < 3; ++i) t(i) = t_[i];
@@ -307,6 +337,7 @@ private:
     int max_iter;
     const double threshold = 1e-5;   // src/cpu.hh:113
     icp_ctx* ctx = nullptr;
+    icp_group* grp = nullptr;        // ICP_DEVICES lists several GPUs
 };
 
 }  // namespace icpb

@@ -33,6 +33,10 @@ EXPORTS = [
     "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
     "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run", "icp_batch_kernels_launched", "icp_release_cached",
     "icp_set_nn_mode", "icp_get_nn_mode",
+    "icp_group_create", "icp_group_destroy", "icp_group_size", "icp_group_member", "icp_group_set_model", "icp_group_set_scene",
+    "icp_group_reset_scene", "icp_group_set_nn_mode", "icp_group_closest", "icp_group_centroid", "icp_group_find_alignment",
+    "icp_group_err_compute", "icp_group_run", "icp_group_get_scene", "icp_group_get_indices", "icp_group_get_transform",
+    "icp_group_get_stats", "icp_batch_run_multi",
 ]
 
 
@@ -101,6 +105,26 @@ def load_library(path=None):
     L.icp_batch_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
                                 C.POINTER(C.c_int64), C.c_int, C.c_double, C.c_int, _ip, _dp, C.c_void_p, _dp]
     L.icp_batch_kernels_launched.restype = C.c_longlong
+    L.icp_batch_run_multi.argtypes = [C.POINTER(C.c_int), C.c_int] + list(L.icp_batch_run.argtypes[1:])
+    L.icp_group_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
+    L.icp_group_destroy.argtypes = [vp]
+    L.icp_group_destroy.restype = None
+    L.icp_group_size.argtypes = [vp]
+    L.icp_group_member.argtypes = [vp, C.c_int]
+    L.icp_group_member.restype = vp
+    L.icp_group_set_model.argtypes = [vp, _dp, C.c_int64]
+    L.icp_group_set_scene.argtypes = [vp, _dp, C.c_int64]
+    L.icp_group_reset_scene.argtypes = [vp]
+    L.icp_group_set_nn_mode.argtypes = [vp, C.c_int]
+    L.icp_group_closest.argtypes = [vp, _ip, _dp]
+    L.icp_group_centroid.argtypes = [vp, _dp, _dp]
+    L.icp_group_find_alignment.argtypes = [vp, _dp, _dp, _dp, _dp]
+    L.icp_group_err_compute.argtypes = [vp, C.c_int, _dp]
+    L.icp_group_run.argtypes = [vp, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int), _dp]
+    L.icp_group_get_scene.argtypes = [vp, _dp]
+    L.icp_group_get_indices.argtypes = [vp, _ip]
+    L.icp_group_get_transform.argtypes = [vp, _dp, _dp, _dp]
+    L.icp_group_get_stats.argtypes = [vp, C.POINTER(IcpStats)]
     L.icp_comm_peer_handle.argtypes = [vp, C.c_void_p]
     L.icp_comm_peer_attach.argtypes = [vp, C.c_void_p, C.c_int, C.c_int]
     _lib = L
@@ -255,9 +279,105 @@ class Context:
         _ck(self._L.icp_comm_peer_attach(self._h, buf, int(rank), int(world)))
 
 
-def batch_run(models, scenes, max_iter=30, threshold=1e-5, check_sizes=True, device=0, lanes=3, want_scene=True):
+class Group:
+    """One process, several GPUs (icp_group_*): the model replicated, the scene cut into contiguous blocks, the
+    per-iteration exchange inside the alignment kernels through peer memory.  Mirrors Context call for call."""
+
+    def __init__(self, devices):
+        self._L = load_library()
+        self._h = C.c_void_p()
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        _ck(self._L.icp_group_create(C.byref(self._h), devs, len(devices)))
+        self.devices = list(devices)
+        self.np = 0
+        self.nm = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.icp_group_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_model(self, m):
+        m = _pts(m)
+        _ck(self._L.icp_group_set_model(self._h, _d(m), len(m)))
+        self.nm = len(m)
+
+    def set_scene(self, p):
+        p = _pts(p)
+        _ck(self._L.icp_group_set_scene(self._h, _d(p), len(p)))
+        self.np = len(p)
+
+    def reset_scene(self):
+        _ck(self._L.icp_group_reset_scene(self._h))
+
+    def set_nn_mode(self, mode):
+        _ck(self._L.icp_group_set_nn_mode(self._h, {"brute": 0, "tree": 1}[mode]))
+
+    def closest(self, want_idx=True, want_Y=True):
+        idx = np.empty(self.np, np.int32) if want_idx else None
+        Y = np.empty((self.np, 3)) if want_Y else None
+        _ck(self._L.icp_group_closest(self._h, _i(idx) if want_idx else None, _d(Y) if want_Y else None))
+        return idx, Y
+
+    def run(self, max_iter, threshold=1e-5, check_sizes=True):
+        it = C.c_int()
+        hist = np.zeros(max(int(max_iter), 1))
+        _ck(self._L.icp_group_run(self._h, int(max_iter), float(threshold), int(bool(check_sizes)), C.byref(it), _d(hist)))
+        return it.value, hist[:it.value].copy()
+
+    def centroid(self):
+        a, b = np.empty(3), np.empty(3)
+        _ck(self._L.icp_group_centroid(self._h, _d(a), _d(b)))
+        return a, b
+
+    def find_alignment(self):
+        s = np.zeros(1); e = np.zeros(1); R = np.empty(9); t = np.empty(3)
+        _ck(self._L.icp_group_find_alignment(self._h, _d(s), _d(R), _d(t), _d(e)))
+        return dict(s=float(s[0]), R=R.reshape(3, 3), t=t, err=float(e[0]))
+
+    def err_compute(self, in_place=True):
+        e = np.zeros(1)
+        _ck(self._L.icp_group_err_compute(self._h, int(bool(in_place)), _d(e)))
+        return float(e[0])
+
+    def get_scene(self, out=None):
+        if out is None:
+            out = np.empty((self.np, 3))
+        assert out.dtype == np.float64 and out.shape == (self.np, 3) and out.flags.c_contiguous
+        _ck(self._L.icp_group_get_scene(self._h, _d(out)))
+        return out
+
+    def indices(self):
+        idx = np.empty(self.np, np.int32)
+        _ck(self._L.icp_group_get_indices(self._h, _i(idx)))
+        return idx
+
+    def transform(self):
+        s = np.zeros(1); R = np.empty(9); t = np.empty(3)
+        _ck(self._L.icp_group_get_transform(self._h, _d(s), _d(R), _d(t)))
+        return float(s[0]), R.reshape(3, 3), t
+
+    def stats(self):
+        st = IcpStats()
+        _ck(self._L.icp_group_get_stats(self._h, C.byref(st)))
+        return st.as_dict()
+
+    def member_stats(self, i):
+        st = IcpStats()
+        _ck(self._L.icp_get_stats(self._L.icp_group_member(self._h, int(i)), C.byref(st)))
+        return st.as_dict()
+
+
+def batch_run(models, scenes, max_iter=30, threshold=1e-5, check_sizes=True, device=0, lanes=3, want_scene=True, devices=None):
     """Registers scenes[k] onto models[k] for every k (independent pairs, reference loop src/cpu.cc:55-79).
-    Returns dict(iters, err, srt[, new_p])."""
+    devices: a list of GPUs of this process to deal the pairs to (icp_batch_run_multi); default: `device` alone.
+    Returns dict(iters, err, srt, kernels_launched[, new_p])."""
     L = load_library()
     n = len(models)
     ms = [_pts(a) for a in models]
@@ -272,8 +392,13 @@ def batch_run(models, scenes, max_iter=30, threshold=1e-5, check_sizes=True, dev
     srt = np.zeros((max(n, 1), 13))
     outs = [np.empty_like(a) for a in ps] if want_scene else []
     op = PP(*[_d(a) for a in outs]) if want_scene else None
-    _ck(L.icp_batch_run(int(device), int(lanes), n, mp, nm, pp, npts, int(max_iter), float(threshold),
-                        int(bool(check_sizes)), _i(iters), _d(err), op, _d(srt)))
+    if devices is not None and len(devices) > 1:
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        _ck(L.icp_batch_run_multi(devs, len(devices), int(lanes), n, mp, nm, pp, npts, int(max_iter), float(threshold),
+                                  int(bool(check_sizes)), _i(iters), _d(err), op, _d(srt)))
+    else:
+        _ck(L.icp_batch_run(int(devices[0] if devices else device), int(lanes), n, mp, nm, pp, npts, int(max_iter), float(threshold),
+                            int(bool(check_sizes)), _i(iters), _d(err), op, _d(srt)))
     res = dict(iters=iters[:n], err=err[:n], srt=srt[:n], kernels_launched=int(L.icp_batch_kernels_launched()))
     if want_scene:
         res["new_p"] = outs

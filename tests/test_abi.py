@@ -56,6 +56,13 @@ def test_no_cpu_fallback_without_device():
     assert b"no CPU fallback" in L.icp_last_error()
     with pytest.raises(icp_b200.IcpError):
         icp_b200.closest_matrix([[0.0, 0, 0]], [[1.0, 0, 0]])
+    with pytest.raises(icp_b200.IcpError) as e:            # the multi-device form fails the same way, and frees what it made
+        icp_b200.Group([0, 1])
+    assert e.value.code == icp_b200.ERR_NO_DEVICE
+    for bad in ([], [0, 0], list(range(17))):
+        with pytest.raises(icp_b200.IcpError) as e:
+            icp_b200.Group(bad)
+        assert e.value.code == icp_b200.ERR_INVALID
 
 
 def test_product_does_not_touch_the_oracle():

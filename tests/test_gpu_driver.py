@@ -70,3 +70,23 @@ def test_tree_search_driver_writes_the_same_bytes(tmp_path, cloud_dir):
     assert ra.returncode == rb.returncode == 0
     assert ra.stderr == rb.stderr and ra.stdout == rb.stdout
     assert (tmp_path / "a" / "output.txt").read_bytes() == (tmp_path / "b" / "output.txt").read_bytes()
+
+
+def test_two_gpu_driver_writes_the_same_bytes(tmp_path, cloud_dir):
+    # ICP_DEVICES=0,1: the drop-in `icp` driver shards the scene over two GPUs of its own process (icp_group_*); the
+    # 18 moment sums are then added in a different order (per-device partials, rank order), so the printed 6-digit
+    # error values and output.txt must agree with the one-GPU run (byte for byte unless a 6th digit sits on a rounding edge)
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ref, scene = cloud_text_path("cow_ref", cloud_dir), cloud_text_path("cow_tr1", cloud_dir)
+    (tmp_path / "a").mkdir()
+    (tmp_path / "b").mkdir()
+    ra = run_icp([ref, scene, "10"], tmp_path / "a")
+    rb = run_icp([ref, scene, "10"], tmp_path / "b", env={"ICP_DEVICES": "0,1"})
+    assert ra.returncode == rb.returncode == 0, rb.stderr
+    la, lb = ra.stderr.splitlines(), rb.stderr.splitlines()
+    assert len(la) == len(lb) and sum(x != y for x, y in zip(la, lb)) <= 1
+    a = (tmp_path / "a" / "output.txt").read_text().splitlines()
+    b = (tmp_path / "b" / "output.txt").read_text().splitlines()
+    assert len(a) == len(b) == 2904 and sum(x != y for x, y in zip(a, b)) <= 5
