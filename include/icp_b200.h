@@ -139,6 +139,9 @@ int icp_get_stats(icp_ctx* ctx, icp_stats* out);
  * the LAST block; slot 0 = microseconds between the end of the preceding nearest-neighbour kernel and entry (large
  * models only: nn_exact stamps it); slots 8, 9 split step 4: partials re-read, block sum done. */
 int icp_get_trace(icp_ctx* ctx, double out_us[10]);
+/* Same diagnostic, per block: for each of the first 32 blocks of that kernel (SM id, then microseconds after block 0's
+ * entry of: own entry, grid barrier passed, Horn solve done, exit); -1 = not stamped. */
+int icp_get_block_trace(icp_ctx* ctx, double out[160]);
 
 /* ---- stateless one-shot forms (host pointers in, host results out) — back the reference-shaped
  * wrappers of src/GPU/gpu.hh:110-116.  Stateless for the caller; internally each host thread keeps one hidden

@@ -83,7 +83,8 @@ __device__ bool peer_allreduce(const PeerComm& pc, const double* vals, int n, do
     if (lane < pc.world) {
         PeerMailbox* dst = pc.box[lane];             // post to rank `lane` (own mailbox included)
         for (int i = 0; i < n; ++i) dst->data[par][pc.rank][i] = vals[i];
-        __threadfence_system();
+        // the data stores above are this thread's own: the system-scope RELEASE of the flag orders them before it for
+        // any reader that acquires the flag (round 1 had a full __threadfence_system() here as well: one fence too many)
         st_release_sys(&dst->flag[par][pc.rank], seq);
         // wait for rank `lane`'s post in my own mailbox
         PeerMailbox* mine = pc.box[pc.rank];
@@ -553,7 +554,10 @@ __global__ void finish_kernel(const double* __restrict__ err_sum, double n_globa
 //            mailboxes, publishes the global sums, second grid barrier, then every block solves.
 //   phase T  q = sR p + t, residual; in_place writes new_p and its FP32 shadow  -> partials_err[block]
 //   last block (ticket): total residual (+ peer exchange), closes the iteration when `finish`.
-__global__ void __launch_bounds__(RED_THREADS, 2)
+#ifndef ICP_FUSED_MIN_CTAS
+#define ICP_FUSED_MIN_CTAS 2
+#endif
+__global__ void __launch_bounds__(RED_THREADS, ICP_FUSED_MIN_CTAS)
 align_fused_kernel(const Pt64* __restrict__ m64, int nm,
                    const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
                    double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
@@ -565,7 +569,15 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     if (honor_done && ctl[CTL_DONE]) return;                 // uniform over the grid: nobody reaches a barrier
     // diagnostic (ICP_PROFILE=1): block 0 stamps %globaltimer at its phase boundaries
 #define TRACE(slot) do { if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[slot] = globaltimer_ns(); } while (0)
+    // ... and the first 32 blocks stamp (SM id, entry, barrier passed, solve done, exit) at trace[16 + 5 b ...]
+#define BTRACE(i) do { if (trace && blockIdx.x < 32 && threadIdx.x == 0) trace[16 + 5 * blockIdx.x + (i)] = globaltimer_ns(); } while (0)
     TRACE(0);
+    if (trace && blockIdx.x < 32 && threadIdx.x == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        trace[16 + 5 * blockIdx.x] = smid;
+    }
+    BTRACE(1);
     cg::grid_group grid = cg::this_grid();
     __shared__ double red[17 * (RED_THREADS / 32)];
     __shared__ double mom_s[MOM_N];
@@ -589,6 +601,7 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     TRACE(2);
     grid.sync();
     TRACE(3);
+    BTRACE(2);
 
     // ---- phase S ------------------------------------------------------------------------------
     if (pc.world == 0 || blockIdx.x == 0) {
@@ -632,6 +645,7 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     }
     __syncthreads();
     TRACE(5);
+    BTRACE(3);
 
     // ---- phase T ------------------------------------------------------------------------------
     const double s = xf_s[0];
@@ -678,6 +692,8 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
         }
     }
     TRACE(7);
+    BTRACE(4);
+#undef BTRACE
 #undef TRACE
 }
 

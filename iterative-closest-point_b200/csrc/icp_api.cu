@@ -84,6 +84,8 @@ NcclApi g_nccl;
 }  // namespace
 
 
+constexpr int TRACE_WORDS = 16 + 5 * 32;   // block 0's phase stamps + (SM id, entry, barrier, solve, exit) of the first 32 blocks
+
 struct icp_ctx {
     int device = 0, sm_count = 148;
     cudaStream_t st = nullptr;
@@ -263,9 +265,16 @@ int allreduce(icp_ctx* c, double* buf, size_t n)
     return ICP_OK;
 }
 
-// Models up to this size are rescanned for undecided points inside nn_refine (no nn_exact launch); larger ones queue
-// them for nn_exact, which shares one scan of the model between four queued points of any block.
-constexpr int64_t INLINE_EXACT_MAX_NM = 131072;
+// An undecided scene point is rescanned over the chunk ranges of the slots that can hold its nearest neighbour (typically
+// one or two).  While such a range is short the block of nn_refine that met the point does it on the spot (no nn_exact
+// launch: 3 kernels per iteration); long ranges are queued for nn_exact, which spreads the points over the whole GPU.
+constexpr long long INLINE_EXACT_MAX_RANGE = 16384;     // model points per slot range
+int inline_exact(const icp_ctx* c)
+{
+    const long long total = (c->s.np_pad / NN_TILE) * (c->m.nm_pad / NN_G);
+    const long long per_cta = (total + c->sc.n_cta - 1) / (c->sc.n_cta > 0 ? c->sc.n_cta : 1);
+    return per_cta * NN_G <= INLINE_EXACT_MAX_RANGE;
+}
 
 // One closest-matrix pass (K1) on the stream.  use_prev: idx[] holds valid matches of the same model (tree mode
 // starts every search from them).
@@ -283,15 +292,15 @@ void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent
             launch_nn_tree(c->m, c->s, c->tree, use_prev, c->d_ctl, honor_done, c->st, c->progress_arg);
         c->stats.kernels_launched += 1;
     } else {
-        const int inline_exact = c->m.nm <= INLINE_EXACT_MAX_NM;
+        const int inl = inline_exact(c);
         launch_nn_filter(c->m, c->s, c->sc, c->d_ctl, honor_done, c->st, c->progress_arg);
         if (e1) cudaEventRecord(e1, c->st);
-        launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, inline_exact, c->st);
+        launch_nn_refine(c->m, c->s, c->sc, c->d_ctl, honor_done, inl, c->st);
         if (e2) cudaEventRecord(e2, c->st);
         e1 = e2 = nullptr;
-        if (!inline_exact)
+        if (!inl)
             launch_nn_exact(c->m, c->s, c->sc, c->d_ctl, honor_done, c->sm_count, c->st, c->profile ? c->d_trace : nullptr);
-        c->stats.kernels_launched += inline_exact ? 2 : 3;
+        c->stats.kernels_launched += inl ? 2 : 3;
     }
     // Model point 0 is NaN: d(0) is NaN for every scene point and minCoeff's strict `<` never replaces it
     // (src/cpu.cc:21-22), so the reference matches everything to index 0; the kernels above ignore NaN candidates.
@@ -354,8 +363,9 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
     // auto: the cooperative kernel where it was measured faster (one GPU, nothing else on it: 11.17 vs 11.27 ms per
     // horse loop), the split pair with peers (its second grid barrier costs more than a launch: 11.65 vs 11.61 ms
     // at N = 2) and in batch lanes (no co-residency requirement between concurrent contexts).
-    // Large scenes take the split pair as well: no co-residency limit on the grid (2^22 points: 225 vs 245 us).
-    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->in_group && !c->is_lane && c->s.np <= 262144);
+    // (Measured again in round 2 with the 32-byte model records: the fused kernel wins at every size on one GPU -
+    // horse 18.9 vs 25.1 us, 2^18 points 23.2 vs 35.9 us, 2^22 points 158 vs 181 us, profiles/r02b_prof_tail_*.log.)
+    const bool fused = c->align_mode == 1 || (c->align_mode == 0 && !c->comm && !c->in_group && !c->is_lane);
     if (fused) {
         const int e = launch_align_fused(c->m, c->s, c->d_partials, fused_blocks(c), c->d_mom, c->d_xf, c->d_err_sum,
                                          c->d_ctl, honor_done, in_place, finish, n_global, threshold, c->d_err_hist, peers,
@@ -418,9 +428,9 @@ static int create_body(icp_ctx* c, int device)
     int r;
     if ((r = dalloc(&c->d_mom, MOM_N)) || (r = dalloc(&c->d_xf, XF_N)) || (r = dalloc(&c->d_err_sum, 1)) ||
         (r = dalloc(&c->d_out6, 8)) || (r = dalloc(&c->d_ctl, CTL_N)) || (r = dalloc(&c->m.geo, 16)) ||
-        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 18)) || (r = dalloc(&c->d_trace, 16)))
+        (r = dalloc(&c->d_partials, (size_t)c->sm_count * 4 * 18)) || (r = dalloc(&c->d_trace, TRACE_WORDS)))
         return r;
-    CK(cudaMemset(c->d_trace, 0, 16 * sizeof(unsigned long long)));
+    CK(cudaMemset(c->d_trace, 0, TRACE_WORDS * sizeof(unsigned long long)));
     c->align_blocks_max = align_fused_max_blocks(c->sm_count);
     if (const char* e = getenv("ICP_COMM")) c->force_nccl = !strcmp(e, "nccl");
     if (const char* e = getenv("ICP_ALIGN")) c->align_mode = !strcmp(e, "fused") ? 1 : (!strcmp(e, "split") ? 2 : 0);
@@ -471,7 +481,6 @@ void icp_destroy(icp_ctx* c)
     dfree(c->s.p64x); dfree(c->s.p64y); dfree(c->s.p64z); dfree(c->s.q64x); dfree(c->s.q64y); dfree(c->s.q64z);
     dfree(c->s.phx); dfree(c->s.phy); dfree(c->s.phz); dfree(c->s.perm); dfree(c->s.idx);
     dfree(c->sc.best); dfree(c->sc.runner); dfree(c->sc.chunk); dfree(c->sc.amb_list); dfree(c->sc.amb_thr);
-    dfree(c->sc.seg_v); dfree(c->sc.seg_k); dfree(c->sc.batch_ticket);
     dfree(c->d_stage); dfree(c->d_partials); dfree(c->d_mom); dfree(c->d_xf); dfree(c->d_err_sum); dfree(c->d_out6);
     dfree(c->d_err_hist); dfree(c->d_ctl); dfree(c->d_keys); dfree(c->d_keys_alt); dfree(c->d_vals);
     dfree(c->d_idx_out); dfree(c->d_vals_alt); dfree(c->tree.nodes); dfree(c->tree.pts); dfree(c->tree.wboxes); dfree(c->tree.wpts);
@@ -543,13 +552,6 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
             (r = dalloc(&c->s.idx, (size_t)np_pad)) || (r = dalloc(&c->sc.amb_list, (size_t)np_pad)) ||
             (r = dalloc(&c->sc.amb_thr, (size_t)np_pad)))
             return r;
-        // nn_exact scratch: per (model segment, queued point) minima + one ticket per batch of queued points
-        c->sc.seg_cap = (size_t)np_pad + 65536;
-        const size_t n_tickets = (size_t)np_pad / nn_exact_batch_points() + 2;
-        if ((r = dalloc(&c->sc.seg_v, c->sc.seg_cap)) || (r = dalloc(&c->sc.seg_k, c->sc.seg_cap)) ||
-            (r = dalloc(&c->sc.batch_ticket, n_tickets)))
-            return r;
-        CK(cudaMemsetAsync(c->sc.batch_ticket, 0, n_tickets * sizeof(int), c->st));
         c->cap_np = (size_t)np_pad;
     }
     // Morton sort of the scene (once per scene; a similarity transform keeps tiles compact)
@@ -859,6 +861,20 @@ int icp_get_trace(icp_ctx* c, double out_us[10])
     if (t[9] >= t[0]) out_us[7] = (double)(t[9] - t[0]) * 1e-3;         // exit of the LAST block instead of block 0
     out_us[8] = t[10] >= t[0] ? (double)(t[10] - t[0]) * 1e-3 : 0.0;
     out_us[9] = t[11] >= t[0] ? (double)(t[11] - t[0]) * 1e-3 : 0.0;
+    return ICP_OK;
+}
+
+int icp_get_block_trace(icp_ctx* c, double out[160])
+{
+    if (!c || !out) return ICP_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    unsigned long long t[TRACE_WORDS];
+    CK(cudaMemcpyAsync(t, c->d_trace, sizeof(t), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    for (int b = 0; b < 32; ++b) {
+        out[5 * b] = (double)t[16 + 5 * b];
+        for (int i = 1; i < 5; ++i) out[5 * b + i] = t[16 + 5 * b + i] >= t[0] && t[16 + 5 * b + i] ? (double)(t[16 + 5 * b + i] - t[0]) * 1e-3 : -1.0;
+    }
     return ICP_OK;
 }
 

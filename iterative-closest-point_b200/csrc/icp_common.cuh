@@ -104,10 +104,6 @@ struct NNScratch {
     uint32_t* chunk = nullptr;
     int32_t* amb_list = nullptr; // [np]   scene points the chunk test could not decide ...
     float* amb_thr = nullptr;    // [np]   ... with their FP32 acceptance threshold best + tau
-    double* seg_v = nullptr;     // [seg_cap] per (model segment, queued point) minima of nn_exact
-    int32_t* seg_k = nullptr;
-    int* batch_ticket = nullptr; // [np / EX_P + 1], self-cleaning
-    size_t seg_cap = 0;
     size_t cap_points = 0;       // allocated n_splits * np_pad
 };
 
@@ -141,7 +137,6 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
                       int inline_exact, cudaStream_t st);
 void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, int* ctl, int honor_done,
                      int sm_count, cudaStream_t st, unsigned long long* trace = nullptr);
-int nn_exact_batch_points();
 // tree search (tree_kernels.cu).  tree_build builds ONE form (wide or binary) and returns a cudaError_t; use_prev: idx[] holds the previous matches.
 size_t tree_sort_bytes(int n);
 int tree_build(const ModelDev& m, TreeDev& t, bool wide, uint32_t* keys, uint32_t* keys_alt,

@@ -90,6 +90,16 @@ __device__ __forceinline__ int cta_of_unit(long long x, long long T, int n)     
     return (int)(((x + 1) * n - 1) / T);
 }
 
+// Chunks [c_lo, c_hi) of scene tile `tile` that its slot `slot` covers: the same integers nn_filter_kernel walks.
+__device__ __forceinline__ void slot_chunks(int tile, int slot, long long T, int n_cta, int cpt, int& c_lo, int& c_hi)
+{
+    const long long x0 = (long long)tile * cpt;
+    const long long b = (long long)cta_of_unit(x0, T, n_cta) + slot;
+    const long long begin = b * T / n_cta, end = (b + 1) * T / n_cta;
+    c_lo = (int)((begin > x0 ? begin : x0) - x0);
+    c_hi = (int)((end < x0 + cpt ? end : x0 + cpt) - x0);
+}
+
 __global__ void __launch_bounds__(NN_THREADS, NN_MIN_CTAS)
 nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx, const float* __restrict__ phy,
                  const float* __restrict__ phz, int np_pad, int n_tiles, int cpt,
@@ -374,22 +384,53 @@ static_assert(RF == 4 || RF == 8 || RF == 16, "RF");
 static_assert(NN_G / RF <= 32, "nn_refine keeps one candidate bit per (lane, step) of the best chunk in a 32-bit mask");
 constexpr int RF_PPW = 32 / RF;                              // scene points per warp
 constexpr int RF_PPB = (REFINE_THREADS / 32) * RF_PPW;       // scene points per block and trip (32)
-#ifndef ICP_IN_P
-#define ICP_IN_P 2
-#endif
-constexpr int IN_P = ICP_IN_P;  // undecided points per in-kernel scan of nn_refine
+
+// Rescan for ONE undecided scene point j by the whole block.  Every model point that can be the reference's argmin has
+// surrogate d' <= thr, and the filter left, per slot of j's scene tile, the exact minimum of that very surrogate over
+// the slot's chunk range: a slot whose minimum is above thr holds no candidate and is skipped.  On horse that leaves
+// one or two of 15 slots (~3 500 of 48 485 model points), on 2^22 points one or two of 66 (round 2; round 1 rescanned
+// the whole model).  NaN / +inf thresholds skip nothing.  Result (first minimum, or NO_INDEX) valid in thread 0.
+__device__ __forceinline__ int pruned_rescan(const float4* __restrict__ mhat, const Pt64* __restrict__ m64, int nm, int nm_pad,
+                                             const float* __restrict__ phx, const float* __restrict__ phy,
+                                             const float* __restrict__ phz, const double* __restrict__ p64x,
+                                             const double* __restrict__ p64y, const double* __restrict__ p64z,
+                                             const float* __restrict__ part_best, int np_pad, int n_tiles, int cpt, int n_cta,
+                                             int j, float thr, double (*sp)[3], double (*sv)[SCAN_THREADS / 32],
+                                             int (*sk)[SCAN_THREADS / 32])
+{
+    ScanPoint q[1];
+    q[0] = scan_point(phx, phy, phz, j, thr);
+    if (threadIdx.x == 0) { sp[0][0] = p64x[j]; sp[0][1] = p64y[j]; sp[0][2] = p64z[j]; }
+    __syncthreads();
+    Best64 bt[1];
+    bt[0].init();
+    const int tile = j / NN_TILE;
+    const long long T = (long long)n_tiles * cpt, x0 = (long long)tile * cpt;
+    const int n_slots = cta_of_unit(x0 + cpt - 1, T, n_cta) - cta_of_unit(x0, T, n_cta) + 1;
+    for (int s = 0; s < n_slots; ++s) {                       // ascending slots = ascending model indices
+        const float sb = part_best[(size_t)s * np_pad + j];   // block-uniform
+        if (sb > thr) continue;
+        int c_lo, c_hi;
+        slot_chunks(tile, s, T, n_cta, cpt, c_lo, c_hi);
+        scan_model<1>(mhat, m64, nm_pad, c_lo * NN_G, min(c_hi * NN_G, nm), q, sp, bt);
+    }
+    double v[1];
+    int k[1];
+    block_argmin<1>(bt, sv, sk, v, k);                        // ends with a barrier: sp / sv / sk are free again
+    return k[0];
+}
 
 // nn_refine: merges the model splits, derives the bound tau and the FP32 acceptance threshold
 // thr = best + tau (rounded up).  Every model point that can be the reference's argmin has d' <= thr.
 //  - runner > thr ("clear"): all such points lie in the best chunk.  Its NN_G points are re-scored with the
 //    FP32 surrogate; only those with d' <= thr (typically one) are evaluated in FP64 with the
 //    reference's own expression, first minimum wins.
-//  - otherwise the point is undecided and the WHOLE model is rescanned against its threshold:
-//      inline_exact = 1 (models up to 131 072 points): right here, by the block that met the point (round 1 queued
-//        these for a separate kernel: on horse that launch served ~85 points per pass and cost 20 us of the 370 us
-//        iteration; the in-kernel scan of 48 485 model points by 256 threads takes ~2 us and only delays its own block);
-//      inline_exact = 0 (large models, where a scan is worth sharing between points of different blocks): the point is
-//        queued with its threshold for nn_exact.
+//  - otherwise the point is undecided and the model is rescanned against its threshold (pruned_rescan):
+//      inline_exact = 1 (a slot's chunk range is short: up to 16 384 model points): right here, by the block that met
+//        the point (round 1 queued these for a separate kernel: on horse that launch served ~85 points per pass and
+//        cost 20 us of the 370 us iteration);
+//      inline_exact = 0 (long ranges, worth spreading over the whole GPU): the point is queued with its threshold for
+//        nn_exact.
 __global__ void __launch_bounds__(REFINE_THREADS, 4)
 nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, int nm_pad,
                  const double* __restrict__ geo,
@@ -404,9 +445,9 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
     __shared__ int s_cnt;
     __shared__ int s_j[RF_PPB];
     __shared__ float s_thr[RF_PPB];
-    __shared__ double sp[IN_P][3];
-    __shared__ double sv[IN_P][SCAN_THREADS / 32];
-    __shared__ int sk[IN_P][SCAN_THREADS / 32];
+    __shared__ double sp[1][3];
+    __shared__ double sv[1][SCAN_THREADS / 32];
+    __shared__ int sk[1][SCAN_THREADS / 32];
     const int lane = threadIdx.x & 31, sub = lane & (RF - 1), grp = lane / RF, w = threadIdx.x >> 5;
     const float Rm = __double2float_ru(geo[3]);
     const float INF = __int_as_float(0x7f800000);
@@ -513,35 +554,14 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
         }
 
         if (inline_exact) {
-            // ---- the block rescans the whole model for the points of this trip it could not decide ----
+            // ---- the block rescans the model for the points of this trip it could not decide ----
             __syncthreads();
             const int nq = s_cnt;                    // block-uniform
-            for (int a0 = 0; a0 < nq; a0 += IN_P) {
-                ScanPoint q[IN_P];
-#pragma unroll
-                for (int p = 0; p < IN_P; ++p) {
-                    const int a = min(a0 + p, nq - 1);          // ragged last batch: duplicates, results dropped
-                    q[p] = scan_point(phx, phy, phz, s_j[a], s_thr[a]);
-                }
-                if (threadIdx.x < IN_P) {
-                    const int jq = s_j[min(a0 + (int)threadIdx.x, nq - 1)];
-                    sp[threadIdx.x][0] = p64x[jq];
-                    sp[threadIdx.x][1] = p64y[jq];
-                    sp[threadIdx.x][2] = p64z[jq];
-                }
-                __syncthreads();
-                Best64 bt[IN_P];
-#pragma unroll
-                for (int p = 0; p < IN_P; ++p) bt[p].init();
-                scan_model<IN_P>(mhat, m64, nm_pad, 0, nm, q, sp, bt);
-                double v[IN_P];
-                int k[IN_P];
-                block_argmin<IN_P>(bt, sv, sk, v, k);
-                if (threadIdx.x == 0) {
-#pragma unroll
-                    for (int p = 0; p < IN_P; ++p)
-                        if (a0 + p < nq) idx[s_j[a0 + p]] = first_min_or_zero(k[p]);
-                }
+            for (int a = 0; a < nq; ++a) {
+                const int jq = s_j[a];
+                const int k = pruned_rescan(mhat, m64, nm, nm_pad, phx, phy, phz, p64x, p64y, p64z, part_best, np_pad, n_tiles,
+                                            cpt, n_cta, jq, s_thr[a], sp, sv, sk);
+                if (threadIdx.x == 0) idx[jq] = first_min_or_zero(k);
             }
             if (threadIdx.x == 0) undecided += nq;
             __syncthreads();                         // s_j / s_cnt are rewritten by the next trip
@@ -550,103 +570,31 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
     if (inline_exact && threadIdx.x == 0 && undecided > 0) atomicAdd(&ctl[CTL_AMB_TOTAL], undecided);
 }
 
-// nn_exact (large models only, see nn_refine): the queued scene points.  FP32 rescan of the WHOLE model with the
-// filter's surrogate; every model point with d' <= thr (a superset of the reference's possible argmins)
-// is evaluated in FP64 with the reference's expression; first minimum wins.
-// Work item = (batch of EX_P queued points) x (model segment); a model point is loaded once per batch.
-// Segment results are merged by the last CTA to finish a batch (ticket per batch).
+// nn_exact (long slot ranges only, see nn_refine): the queued scene points, one per block at a time (grid-stride over
+// the queue), each rescanned with pruned_rescan.  Round 1 rescanned the whole model for batches of four queued points
+// cut into model segments with a ticket merge; with the slot pruning a point needs 1-2 ranges of <= 64 K model points,
+// and the segments, tickets and merge scratch are gone.
 constexpr int EXACT_THREADS = SCAN_THREADS;
-#ifndef ICP_EX_P
-#define ICP_EX_P 4
-#endif
-#ifndef ICP_EX_MIN_SEG
-#define ICP_EX_MIN_SEG 4096
-#endif
-constexpr int EX_P = ICP_EX_P;   // queued points per batch (4; build-time variant like ICP_NN_*)
-constexpr int EX_MIN_SEG = ICP_EX_MIN_SEG; // model points per segment at least (4096; 1024 was measured slower: more tickets and merges)
 
 __global__ void __launch_bounds__(EXACT_THREADS)
 nn_exact_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, int nm_pad,
                 const double* __restrict__ p64x,
                 const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
-                const float* __restrict__ phy, const float* __restrict__ phz, const int32_t* __restrict__ amb_list,
-                const float* __restrict__ amb_thr, int32_t* __restrict__ idx, double* __restrict__ seg_v,
-                int32_t* __restrict__ seg_k, int seg_cap, int* __restrict__ batch_ticket, int* __restrict__ ctl, int np,
+                const float* __restrict__ phy, const float* __restrict__ phz, const float* __restrict__ part_best,
+                int np_pad, int n_tiles, int cpt, int n_cta, const int32_t* __restrict__ amb_list,
+                const float* __restrict__ amb_thr, int32_t* __restrict__ idx, int* __restrict__ ctl,
                 int honor_done, unsigned long long* __restrict__ trace)
 {
     if (honor_done && ctl[CTL_DONE]) return;
-    __shared__ double sp[EX_P][3];
-    __shared__ double sv[EX_P][EXACT_THREADS / 32];
-    __shared__ int sk[EX_P][EXACT_THREADS / 32];
-    __shared__ int s_last;
+    __shared__ double sp[1][3];
+    __shared__ double sv[1][EXACT_THREADS / 32];
+    __shared__ int sk[1][EXACT_THREADS / 32];
     const int count = ctl[CTL_AMB_COUNT];
-    const int n_batches = (count + EX_P - 1) / EX_P;
-    // segments: enough items to fill the grid twice, bounded by the segment floor and the scratch
-    int n_seg = 1;
-    if (n_batches > 0) {
-        n_seg = (2 * (int)gridDim.x + n_batches - 1) / n_batches;
-        n_seg = min(n_seg, max(1, nm / EX_MIN_SEG));
-        n_seg = min(n_seg, max(1, seg_cap / (n_batches * EX_P)));
-    }
-    const int seg_len = ((nm + n_seg - 1) / n_seg + EXACT_THREADS * EX_U - 1) / (EXACT_THREADS * EX_U) * (EXACT_THREADS * EX_U);
-    const int items = n_batches * n_seg;
-    const double DINF = __longlong_as_double(0x7ff0000000000000LL);
-
-    for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        const int batch = item / n_seg, seg = item - batch * n_seg;
-        const int a0 = batch * EX_P;
-        int jj[EX_P];
-        ScanPoint q[EX_P];
-#pragma unroll
-        for (int p = 0; p < EX_P; ++p) {
-            const int a = min(a0 + p, count - 1);          // ragged last batch: duplicates, results dropped
-            jj[p] = amb_list[a];
-            q[p] = scan_point(phx, phy, phz, jj[p], amb_thr[a]);
-        }
-        __syncthreads();                                    // previous item's readers of sp are done
-        if (threadIdx.x < EX_P) {
-            const int j = amb_list[min(a0 + (int)threadIdx.x, count - 1)];
-            sp[threadIdx.x][0] = p64x[j];
-            sp[threadIdx.x][1] = p64y[j];
-            sp[threadIdx.x][2] = p64z[j];
-        }
-        __syncthreads();
-        Best64 bt[EX_P];
-#pragma unroll
-        for (int p = 0; p < EX_P; ++p) bt[p].init();
-        const int k_begin = seg * seg_len, k_end = min(k_begin + seg_len, nm);
-        scan_model<EX_P>(mhat, m64, nm_pad, k_begin, k_end, q, sp, bt);
-        double v[EX_P];
-        int k[EX_P];
-        block_argmin<EX_P>(bt, sv, sk, v, k);
-        if (threadIdx.x == 0) {
-#pragma unroll
-            for (int p = 0; p < EX_P; ++p)
-                if (a0 + p < count) {
-                    if (n_seg == 1) idx[jj[p]] = first_min_or_zero(k[p]);
-                    else { seg_v[(size_t)seg * n_batches * EX_P + a0 + p] = v[p]; seg_k[(size_t)seg * n_batches * EX_P + a0 + p] = k[p]; }
-                }
-        }
-        if (n_seg > 1) {
-            if (threadIdx.x == 0) {
-                __threadfence();
-                const int t = atomicAdd(&batch_ticket[batch], 1);
-                s_last = (t == n_seg - 1);
-                if (s_last) batch_ticket[batch] = 0;
-            }
-            __syncthreads();
-            if (s_last && threadIdx.x < EX_P && a0 + (int)threadIdx.x < count) {
-                __threadfence();
-                double vm = DINF;
-                int km = NO_INDEX;
-                for (int s = 0; s < n_seg; ++s) {
-                    const double ov = __ldcg(&seg_v[(size_t)s * n_batches * EX_P + a0 + threadIdx.x]);
-                    const int ok = __ldcg(&seg_k[(size_t)s * n_batches * EX_P + a0 + threadIdx.x]);
-                    if (ov < vm || (ov == vm && ok < km)) { vm = ov; km = ok; }
-                }
-                idx[amb_list[a0 + threadIdx.x]] = first_min_or_zero(km);
-            }
-        }
+    for (int a = blockIdx.x; a < count; a += gridDim.x) {
+        const int j = amb_list[a];
+        const int k = pruned_rescan(mhat, m64, nm, nm_pad, phx, phy, phz, p64x, p64y, p64z, part_best, np_pad, n_tiles, cpt,
+                                    n_cta, j, amb_thr[a], sp, sv, sk);
+        if (threadIdx.x == 0) idx[j] = first_min_or_zero(k);
     }
     if (threadIdx.x == 0) {
         __threadfence();
@@ -692,11 +640,9 @@ void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, 
 {
     const int grid = sm_count * 4;
     nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64, m.mhat, (int)m.nm, (int)m.nm_pad, s.p64x,
-                                                    s.p64y, s.p64z, s.phx, s.phy, s.phz, sc.amb_list, sc.amb_thr, s.idx,
-                                                    sc.seg_v, sc.seg_k, (int)sc.seg_cap, sc.batch_ticket, ctl,
-                                                    (int)s.np, honor_done, trace);
+                                                    s.p64y, s.p64z, s.phx, s.phy, s.phz, sc.best, (int)s.np_pad,
+                                                    (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.n_cta,
+                                                    sc.amb_list, sc.amb_thr, s.idx, ctl, honor_done, trace);
 }
-
-int nn_exact_batch_points() { return EX_P; }
 
 }  // namespace icpb

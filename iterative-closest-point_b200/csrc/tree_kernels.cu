@@ -497,10 +497,16 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
         if (kp >= 0 && kp < nm) {
             const float4 m = mhat[kp];
             const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
-            q.set_best(d2);
-            if (lane == 0) {
-                q.v = __dsqrt_rn(ref_dist2_pt(q.qx, q.qy, q.qz, m64, kp));
-                q.k = kp;
+            // Only a FINITE surrogate may tighten the threshold: an overflowed one (scene point > 1e19 away) would set
+            // thr2 = +inf, which opens the EMPTY boxes of padded leaves (+inf) - reads past the sorted points (found by
+            // the non-finite-input test of round 2) - and would keep last iteration's match without a search.  Such a
+            // point falls through to the FP64 scan below, like on the first iteration.  NaN (model point 0 is NaN): same.
+            if (d2 <= 3.4028235e38f) {
+                q.set_best(d2);
+                if (lane == 0) {
+                    q.v = __dsqrt_rn(ref_dist2_pt(q.qx, q.qy, q.qz, m64, kp));
+                    q.k = kp;
+                }
             }
         }
     }
@@ -555,6 +561,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
         const int ok = __shfl_xor_sync(FULL, k, o);
         if (ov < v || (ov == v && ok < k)) { v = ov; k = ok; }
     }
+    k = __shfl_sync(FULL, k, 0);  // one decision for the warp (with NaN values the butterfly is not a total order)
     if (k == 0x7fffffff) {       // FP32 surrogate overflowed (scene point > 1e19 away): FP64 scan, first minimum
         v = __longlong_as_double(0x7ff0000000000000LL);
         for (int kk = lane; kk < nm; kk += 32) {

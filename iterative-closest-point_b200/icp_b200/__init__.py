@@ -31,7 +31,7 @@ EXPORTS = [
     "icp_get_scene", "icp_reset_scene", "icp_closest", "icp_centroid", "icp_find_alignment", "icp_err_compute",
     "icp_get_transform", "icp_run", "icp_get_indices", "icp_get_stats", "icp_closest_matrix_host",
     "icp_nearest_index_host", "icp_find_alignment_host", "icp_err_compute_host", "icp_subtract_col_host", "icp_y_p_norm_host",
-    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_batch_run", "icp_batch_kernels_launched", "icp_release_cached",
+    "icp_comm_unique_id", "icp_comm_init", "icp_comm_world", "icp_comm_peer_handle", "icp_comm_peer_attach", "icp_get_trace", "icp_get_block_trace", "icp_batch_run", "icp_batch_kernels_launched", "icp_release_cached",
     "icp_set_nn_mode", "icp_get_nn_mode",
     "icp_group_create", "icp_group_destroy", "icp_group_size", "icp_group_member", "icp_group_set_model", "icp_group_set_scene",
     "icp_group_reset_scene", "icp_group_set_nn_mode", "icp_group_closest", "icp_group_centroid", "icp_group_find_alignment",
@@ -102,6 +102,7 @@ def load_library(path=None):
     L.icp_comm_init.argtypes = [vp, C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     L.icp_comm_world.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.icp_get_trace.argtypes = [vp, _dp]
+    L.icp_get_block_trace.argtypes = [vp, _dp]
     L.icp_batch_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
                                 C.POINTER(C.c_int64), C.c_int, C.c_double, C.c_int, _ip, _dp, C.c_void_p, _dp]
     L.icp_batch_kernels_launched.restype = C.c_longlong
@@ -258,6 +259,12 @@ class Context:
         t = np.zeros(10)
         _ck(self._L.icp_get_trace(self._h, _d(t)))
         return t
+
+    def block_trace(self):
+        """(32, 5): SM id, entry, barrier passed, solve done, exit (us after block 0's entry) of the first 32 blocks."""
+        t = np.zeros(160)
+        _ck(self._L.icp_get_block_trace(self._h, _d(t)))
+        return t.reshape(32, 5)
 
     def comm_init(self, id128, rank, world, nccl_path=None):
         path = nccl_path or torch_nccl_path()

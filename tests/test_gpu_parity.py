@@ -196,6 +196,23 @@ def test_batch_run_matches_oracle_per_pair(icp):
         icp.batch_run([models[0]], [scenes[1]], max_iter=5)
 
 
+def test_batch_run_full_size_pair_matches_oracle(icp):
+    # BASELINE config 5 at its stated point count: one 65 536-point noisy pair of the batch (SURVEY 8d recipe, pair 3)
+    # through icp_batch_run, next to a small pair so that two lanes are busy; iteration count, error history end,
+    # transform and new_p against the oracle's full loop (a few seconds on the host's cores)
+    from icp_b200 import synth
+    m, p = synth.config5_pair(3)
+    ms, ps, _ = synthetic_pair(3000, seed=77)
+    res = icp.batch_run([m, ms], [p, ps], max_iter=30, lanes=2)
+    ro = O.icp_run(m, p, 30)
+    assert res["iters"][0] == ro["iters"]
+    assert abs(res["err"][0] - ro["err"][-1]) <= RTOL * abs(ro["err"][-1])
+    assert np.abs(res["new_p"][0] - ro["new_p"]).max() < 1e-9
+    s_, R_, t_ = res["srt"][0][0], res["srt"][0][1:10].reshape(3, 3), res["srt"][0][10:13]
+    assert abs(s_ - ro["s"][-1]) <= RTOL * abs(ro["s"][-1]) and rel(R_, ro["R"][-1]) <= RTOL and rel(t_, ro["t"][-1]) <= RTOL
+    assert res["kernels_launched"] >= 3 * ro["iters"]
+
+
 @pytest.mark.parametrize("n,seed", [(1000, 0), (5000, 1), (65536, 2)])
 def test_closest_synthetic(icp, n, seed):
     m, p, _ = synthetic_pair(n, seed=seed)

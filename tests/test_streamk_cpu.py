@@ -59,6 +59,14 @@ def segments(b, n_cta, n_tiles, cpt):
         tile += 1
 
 
+def slot_chunks(tile, slot, T, n_cta, cpt):
+    """nn_kernels.cu slot_chunks(): the chunk range a slot of a scene tile covers (what pruned_rescan scans)."""
+    x0 = tile * cpt
+    b = cta_of_unit(x0, T, n_cta) + slot
+    begin, end = b * T // n_cta, (b + 1) * T // n_cta
+    return max(begin, x0) - x0, min(end, x0 + cpt) - x0
+
+
 def check(np_, nm, forced=0):
     n_cta, n_splits = choose_splits(np_, nm, forced)
     n_tiles = pad(np_, NN_TILE) // NN_TILE
@@ -74,6 +82,7 @@ def check(np_, nm, forced=0):
             mt0, mt1 = c_lo // CPM, (c_hi + CPM - 1) // CPM
             assert mt1 * NN_TM <= pad(nm, NN_TM)                  # bulk copies stay inside mhat
             assert b == cta_of_unit(tile * cpt + c_lo, T, n_cta)  # cta_of_unit() inverts the range formula
+            assert slot_chunks(tile, slot, T, n_cta, cpt) == (c_lo, c_hi)   # the rescan of undecided points prunes by slot
     assert (covered == 1).all()
     for tile in range(n_tiles):
         x0 = tile * cpt

@@ -13,6 +13,8 @@ run() {   # name, library
   for w in horse syn256k; do
     timeout 300 python bench.py --skip-cpu-baseline --workload $w --steps 20 --warmup 3 > gpurun_out/ab_$1_$w.json 2> gpurun_out/ab_$1_$w.err
   done
+  # K2 / K4 as HBM-bound passes on 2^22 points (tree search so that the run takes milliseconds): alignment variants only
+  case $1 in fused*|default_a) ICP_NN=tree timeout 300 python tools/prof_tail.py syn4m 3 > gpurun_out/ab_$1_tail.log 2>&1;; esac
 }
 run default_a $LIBDIR/libicp_b200.so
 for v in $V; do [ -f $LIBDIR/variants/libicp_b200_$v.so ] && run $v $LIBDIR/variants/libicp_b200_$v.so; done
@@ -32,3 +34,4 @@ for v in ["default_a"] + sys.argv[1:] + ["default_b"]:
         except Exception as e:
             print("%-14s %-8s failed: %s" % (v, w, e))
 PY
+grep -H "K2+K4" gpurun_out/ab_*_tail.log | tee -a gpurun_out/ab_summary.txt

@@ -35,6 +35,9 @@ def loop_timing(tag, m, p, max_iter=30, check=True):
     print(f"{tag}: loop {it} it  dev {st['ms_total']:.3f} ms (filter {st['ms_filter']:.3f} refine {st['ms_refine']:.3f} exact {st['ms_exact']:.3f} align {st['ms_align']:.3f} ms) wall {dt*1e3:.3f} ms  "
           f"{it/(st['ms_total']*1e-3):.1f} it/s  {it*len(m)*len(p)/(st['ms_total']*1e-3)/1e12:.3f} T evals/s  last err {hist[-1]:.3e}", flush=True)
     if os.environ.get("ICP_PROFILE"):
+        if tag == "cow":
+            bt = ctx.block_trace()
+            print("   per block (SM, entry, barrier, solve, exit us):", " | ".join(" ".join(f"{v:.1f}" for v in r) for r in bt if r[4] >= 0))
         print("   align trace (us: gap after K1 | from entry: moments, partials, barrier, reduce, solve, transform, last block out | partials re-read, block sum):", np.round(ctx.trace(), 2))
     ctx.close()
 
