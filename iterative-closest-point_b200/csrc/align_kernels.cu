@@ -554,8 +554,10 @@ __global__ void finish_kernel(const double* __restrict__ err_sum, double n_globa
 //            mailboxes, publishes the global sums, second grid barrier, then every block solves.
 //   phase T  q = sR p + t, residual; in_place writes new_p and its FP32 shadow  -> partials_err[block]
 //   last block (ticket): total residual (+ peer exchange), closes the iteration when `finish`.
+// 3 CTAs per SM (85 registers; the Horn solve spills a little, once per block): measured against 2 and 4 on 2^22 points,
+// K2+K4 159 / 150 / 156 us (profiles/r02c_ab_summary.txt)
 #ifndef ICP_FUSED_MIN_CTAS
-#define ICP_FUSED_MIN_CTAS 2
+#define ICP_FUSED_MIN_CTAS 3
 #endif
 __global__ void __launch_bounds__(RED_THREADS, ICP_FUSED_MIN_CTAS)
 align_fused_kernel(const Pt64* __restrict__ m64, int nm,
@@ -604,13 +606,22 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     BTRACE(2);
 
     // ---- phase S ------------------------------------------------------------------------------
-    if (pc.world == 0 || blockIdx.x == 0) {
+#ifdef ICP_FUSED_SOLVE_ONE
+    const bool solve_one = true;           // diagnostic build: block 0 alone reduces and solves, the others wait and read xf
+#else
+    const bool solve_one = false;
+#endif
+    if ((pc.world == 0 && !solve_one) || blockIdx.x == 0) {
         double tot[17];
 #pragma unroll
         for (int i = 0; i < 17; ++i) tot[i] = 0.0;
         for (int b = threadIdx.x; b < nb; b += RED_THREADS)
 #pragma unroll
+#ifdef ICP_PARTIALS_LDCV
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcv(&partials[(size_t)i * nb + b]);
+#else
             for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)i * nb + b]);
+#endif
         TRACE(10);
         block_sum<17>(tot, red);
         TRACE(11);
@@ -635,7 +646,16 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
         __syncthreads();
     }
     TRACE(4);
-    if (threadIdx.x == 0) {
+    if (solve_one && pc.world == 0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            horn_solve(geo, mom_s, xf_s);
+            for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];
+            for (int i = 0; i < MOM_N; ++i) mom[i] = mom_s[i];
+            __threadfence();
+        }
+        grid.sync();
+        if (blockIdx.x != 0 && threadIdx.x < XF_N) xf_s[threadIdx.x] = __ldcg(&xf[threadIdx.x]);
+    } else if (threadIdx.x == 0) {
         horn_solve(geo, mom_s, xf_s);
         if (blockIdx.x == 0) {
             for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];

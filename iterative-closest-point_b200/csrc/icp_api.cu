@@ -112,6 +112,7 @@ struct icp_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
+    int exact_mode = 0;                    // ICP_EXACT: 0 auto, 1 always inside nn_refine, 2 always the nn_exact kernel
     bool model0_nan = false;               // model point 0 has a NaN coordinate: the reference's first-minimum scan never leaves it
     size_t cap_nm = 0, cap_np = 0;         // allocated capacities (points): buffers only ever grow
     // fused alignment kernel (cooperative) and the peer-memory exchange it carries when world > 1
@@ -271,6 +272,7 @@ int allreduce(icp_ctx* c, double* buf, size_t n)
 constexpr long long INLINE_EXACT_MAX_RANGE = 16384;     // model points per slot range
 int inline_exact(const icp_ctx* c)
 {
+    if (c->exact_mode) return c->exact_mode == 1;     // ICP_EXACT=inline|kernel: test hook, both forms on any input
     const long long total = (c->s.np_pad / NN_TILE) * (c->m.nm_pad / NN_G);
     const long long per_cta = (total + c->sc.n_cta - 1) / (c->sc.n_cta > 0 ? c->sc.n_cta : 1);
     return per_cta * NN_G <= INLINE_EXACT_MAX_RANGE;
@@ -438,6 +440,13 @@ static int create_body(icp_ctx* c, int device)
     if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
     if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
     if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
+    if (const char* e = getenv("ICP_EXACT")) c->exact_mode = !strcmp(e, "inline") ? 1 : (!strcmp(e, "kernel") ? 2 : 0);
+    // ICP_L2_FETCH=32|64|128 (experiment): the device's L2 fetch granularity hint.  K2 / K4 gather one 32-byte model
+    // record per scene point from an array that does not fit L2; a 64-byte fetch brings a second record nobody asked for.
+    if (const char* e = getenv("ICP_L2_FETCH")) {
+        const int g = atoi(e);
+        if (g == 32 || g == 64 || g == 128) { cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g); cudaGetLastError(); }
+    }
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
@@ -903,6 +912,8 @@ static void apply_env_nn(icp_ctx* c)
 {
     const char* e = getenv("ICP_NN");
     c->nn_mode = (e && !strcmp(e, "tree")) ? ICP_NN_TREE : ICP_NN_BRUTE;
+    e = getenv("ICP_EXACT");
+    c->exact_mode = (e && !strcmp(e, "inline")) ? 1 : ((e && !strcmp(e, "kernel")) ? 2 : 0);
 }
 
 static int oneshot_ctx(icp_ctx** out)

@@ -18,11 +18,11 @@ namespace icpb {
 // ---- nearest-neighbour filter geometry ---------------------------------------------------------
 // The ICP_NN_* macros exist for A/B builds only (`make variants`, tools/filter_ab.sh: one library per variant,
 // selected at run time with ICP_B200_LIB); the product is the defaults.  Round 2 measured the variants the static SASS
-// study of round 1 favoured (profiles/r02a_ab_summary.txt): 12 scene points per thread at 3 CTAs per SM, 128-point
-// chunks and the inner loop unrolled 8x replaced round 1's 8 / 4 / 64 / 2 (horse 0.795 -> 0.833 of the FP32 roofline,
-// 2^18 points 0.858 -> 0.903).
+// study of round 1 favoured and then their neighbours (profiles/r02a_ab_summary.txt, r02b_, r02c_): 16 scene points per
+// thread at 2 CTAs per SM (255 registers, no spills), 128-point chunks and the inner loop unrolled 8x replaced round 1's
+// 8 / 4 / 64 / 2 (filter kernel on horse 0.795 -> 0.852 of the FP32 roofline, on 2^18 points 0.858 -> 0.914).
 #ifndef ICP_NN_R
-#define ICP_NN_R 12
+#define ICP_NN_R 16
 #endif
 #ifndef ICP_NN_G
 #define ICP_NN_G 128
@@ -31,15 +31,15 @@ namespace icpb {
 #define ICP_NN_Q_UNROLL 8
 #endif
 #ifndef ICP_NN_MIN_CTAS
-#define ICP_NN_MIN_CTAS 3
+#define ICP_NN_MIN_CTAS 2
 #endif
 constexpr int NN_THREADS = 128;                 // threads per CTA
-constexpr int NN_R       = ICP_NN_R;            // scene points register-blocked per thread (12)
-constexpr int NN_TILE    = NN_THREADS * NN_R;   // scene points per CTA (1536)
+constexpr int NN_R       = ICP_NN_R;            // scene points register-blocked per thread (16)
+constexpr int NN_TILE    = NN_THREADS * NN_R;   // scene points per CTA (2048)
 constexpr int NN_G       = ICP_NN_G;            // model points per tracking chunk (128)
 constexpr int NN_TM      = 512;                 // model points per shared-memory stage
 constexpr int NN_Q_UNROLL = ICP_NN_Q_UNROLL;    // LDS.128 quadruples per trip of the filter's inner loop (8)
-constexpr int NN_MIN_CTAS = ICP_NN_MIN_CTAS;    // resident filter CTAs per SM the launch bounds ask for (3)
+constexpr int NN_MIN_CTAS = ICP_NN_MIN_CTAS;    // resident filter CTAs per SM the launch bounds ask for (2)
 static_assert(NN_TM % NN_G == 0 && NN_G % 32 == 0 && NN_G <= 256, "chunk size");
 static_assert((NN_G / 4) % NN_Q_UNROLL == 0, "inner-loop unroll must divide the chunk");
 constexpr float NN_SENTINEL = 1.0e18f;          // coordinate of padded model points (never wins)

@@ -80,10 +80,14 @@ def test_closest_near_ties_below_fp32_resolution(icp):
     assert np.array_equal(idx, idx_o)
 
 
-def test_closest_exact_scan_paths(icp):
+@pytest.mark.parametrize("form", ["auto", "inline", "kernel"])
+def test_closest_exact_scan_paths(icp, monkeypatch, form):
     # nn_exact work decomposition: (a) a handful of undecidable points against a model long enough to be cut
     # into several segments (ragged last batch, cross-segment merge by ticket); (b) every scene point
     # undecidable (one segment, many batches); (c) a scene far away from the model (large tau).
+    # ICP_EXACT (read at icp_create, and at every use by the hidden context of the one-shot wrappers) forces the rescan
+    # inside nn_refine or the separate nn_exact kernel, so both forms meet every case whatever the automatic choice is
+    monkeypatch.setenv("ICP_EXACT", form)
     rng = np.random.default_rng(21)
     base = rng.uniform(-1, 1, (20000, 3))
     m = np.concatenate([base, base[:50][::-1]])           # 50 points exist twice, 20 000 indices apart
@@ -107,10 +111,11 @@ def test_closest_exact_scan_paths(icp):
     assert np.array_equal(idx, idx_o)
 
 
-def test_closest_exact_scan_large_model(icp):
-    # models above 131 072 points queue their undecided points for nn_exact (smaller ones are rescanned inside
-    # nn_refine): (a) a few duplicates far apart -> several model segments merged by ticket, ragged last batch;
-    # (b) every scene point undecided -> many batches
+@pytest.mark.parametrize("form", ["auto", "inline", "kernel"])
+def test_closest_exact_scan_large_model(icp, monkeypatch, form):
+    # a model cut into many slots per scene tile: (a) a few duplicates far apart -> two distant slot ranges qualify for
+    # each undecided point; (b) every scene point undecided
+    monkeypatch.setenv("ICP_EXACT", form)
     rng = np.random.default_rng(23)
     base = rng.uniform(-1, 1, (140000, 3))
     m = np.concatenate([base, base[:50][::-1]])

@@ -94,7 +94,7 @@ def test_tree_scale_outside_range_keeps_brute_force(icp):
     m, p = rng.uniform(-1, 1, (2000, 3)) * 1e-15, rng.uniform(-1, 1, (500, 3)) * 1e-15
     idx_o, _ = O.closest_matrix(p, m, O.NN_MULSQRT)
     idx, _, st = tree_closest(icp, p, m, expect_mode="brute")
-    assert np.array_equal(idx, idx_o) and st["kernels_launched"] == 3
+    assert np.array_equal(idx, idx_o) and st["kernels_launched"] == 2      # filter + refine (undecided points rescanned in place)
 
 
 @pytest.mark.parametrize("n,seed", [(5000, 1), (65536, 2)])

@@ -1,6 +1,6 @@
 """CPU model of the filter's work decomposition (csrc/nn_kernels.cu "stream-K", icp_api.cu choose_splits()).
 
-The np_pad/1536 scene tiles x nm_pad/128 model chunks form one linear sequence of T chunk-units; CTA b owns
+The np_pad/2048 scene tiles x nm_pad/128 model chunks form one linear sequence of T chunk-units; CTA b owns
 [b*T/n, (b+1)*T/n), writes one partial result per (CTA, scene tile) segment into slot = b - first CTA of that tile, and
 nn_refine_kernel recomputes the slot count of a tile from the same integers.  This restates that integer arithmetic
 and asserts, over small exhaustive sweeps and the sizes of BASELINE.json's configs, what the kernels rely on:
@@ -14,10 +14,10 @@ and asserts, over small exhaustive sweeps and the sizes of BASELINE.json's confi
 import numpy as np
 import pytest
 
-NN_TILE, NN_G, NN_TM = 1536, 128, 512      # round 2 defaults: 12 scene points per thread, 128-point chunks
+NN_TILE, NN_G, NN_TM = 2048, 128, 512      # round 2 defaults: 16 scene points per thread, 128-point chunks
 CPM = NN_TM // NN_G
 SMS = 148
-MIN_CTAS = 3          # resident filter CTAs per SM (NN_MIN_CTAS)
+MIN_CTAS = 2          # resident filter CTAs per SM (NN_MIN_CTAS)
 
 
 def pad(n, q):
@@ -118,7 +118,7 @@ def test_largest_configuration_fits_the_kernel_state():
     n_cta, n_splits = choose_splits(np_, nm)
     n_tiles, cpt = pad(np_, NN_TILE) // NN_TILE, nm // NN_G
     T = n_tiles * cpt
-    assert (n_tiles, cpt) == (2731, 32768) and n_cta % (SMS * MIN_CTAS) == 0
+    assert (n_tiles, cpt) == (2048, 32768) and n_cta % (SMS * MIN_CTAS) == 0
     assert T // n_cta + 1 < 2 ** 31 and n_cta < 2 ** 31
     assert 450 <= T / n_cta <= 550                                # ranges of ~64 K model points x one scene tile
     assert n_splits * pad(np_, NN_TILE) * 4 < 2 ** 40             # scratch rows: a few hundred MB at most
@@ -129,7 +129,7 @@ def test_largest_configuration_fits_the_kernel_state():
         assert all(0 <= s < n_splits for *_, s in segs)
 
 
-@pytest.mark.parametrize("r,g,ctas", [(8, 64, 4), (8, 128, 4), (12, 64, 3), (12, 256, 3), (16, 128, 2)])
+@pytest.mark.parametrize("r,g,ctas", [(8, 64, 4), (8, 128, 4), (12, 64, 3), (12, 128, 3), (16, 256, 2)])
 def test_variant_geometries(monkeypatch, r, g, ctas):
     """The build-time variants of the filter (icp_common.cuh ICP_NN_R / _G / _MIN_CTAS, `make variants`) run the same
     integer arithmetic with other constants: 128-point chunks, 1 536- and 2 048-point scene tiles, 3 or 2 CTAs per SM."""
@@ -151,9 +151,9 @@ def test_small_clouds_use_every_sm_they_can():
     remain (round 2: cow's filter 35 -> 25 us).  cow = 2 scene tiles x 24 chunks = 48 units -> 48 CTAs of one unit."""
     n_cta, n_splits = check(2903, 2903)
     assert n_cta == 48 and n_splits == 25
-    n_cta, _ = check(8192, 8192)                 # 6 tiles x 64 chunks = 384 units: one CTA per SM, not 96
+    n_cta, _ = check(8192, 8192)                 # 4 tiles x 64 chunks = 256 units: one CTA per SM, not 64
     assert n_cta == SMS
-    n_cta, _ = check(48485, 48485)               # horse: one full wave, ~27 chunks per CTA
+    n_cta, _ = check(48485, 48485)               # horse: one full wave, ~31 chunks per CTA
     assert n_cta == SMS * MIN_CTAS
     for np_ in (1, 1023, 1025, 2903, 5000, 9000):
         for nm in (1, 64, 65, 513, 2903, 4097):
