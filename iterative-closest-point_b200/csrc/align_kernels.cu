@@ -606,22 +606,13 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     BTRACE(2);
 
     // ---- phase S ------------------------------------------------------------------------------
-#ifdef ICP_FUSED_SOLVE_ONE
-    const bool solve_one = true;           // diagnostic build: block 0 alone reduces and solves, the others wait and read xf
-#else
-    const bool solve_one = false;
-#endif
-    if ((pc.world == 0 && !solve_one) || blockIdx.x == 0) {
+    if (pc.world == 0 || blockIdx.x == 0) {
         double tot[17];
 #pragma unroll
         for (int i = 0; i < 17; ++i) tot[i] = 0.0;
         for (int b = threadIdx.x; b < nb; b += RED_THREADS)
 #pragma unroll
-#ifdef ICP_PARTIALS_LDCV
-            for (int i = 0; i < 17; ++i) tot[i] += __ldcv(&partials[(size_t)i * nb + b]);
-#else
             for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)i * nb + b]);
-#endif
         TRACE(10);
         block_sum<17>(tot, red);
         TRACE(11);
@@ -646,16 +637,7 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
         __syncthreads();
     }
     TRACE(4);
-    if (solve_one && pc.world == 0) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            horn_solve(geo, mom_s, xf_s);
-            for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];
-            for (int i = 0; i < MOM_N; ++i) mom[i] = mom_s[i];
-            __threadfence();
-        }
-        grid.sync();
-        if (blockIdx.x != 0 && threadIdx.x < XF_N) xf_s[threadIdx.x] = __ldcg(&xf[threadIdx.x]);
-    } else if (threadIdx.x == 0) {
+    if (threadIdx.x == 0) {
         horn_solve(geo, mom_s, xf_s);
         if (blockIdx.x == 0) {
             for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];

@@ -441,12 +441,6 @@ static int create_body(icp_ctx* c, int device)
     if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
     if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
     if (const char* e = getenv("ICP_EXACT")) c->exact_mode = !strcmp(e, "inline") ? 1 : (!strcmp(e, "kernel") ? 2 : 0);
-    // ICP_L2_FETCH=32|64|128 (experiment): the device's L2 fetch granularity hint.  K2 / K4 gather one 32-byte model
-    // record per scene point from an array that does not fit L2; a 64-byte fetch brings a second record nobody asked for.
-    if (const char* e = getenv("ICP_L2_FETCH")) {
-        const int g = atoi(e);
-        if (g == 32 || g == 64 || g == 128) { cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g); cudaGetLastError(); }
-    }
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
     CK(cudaMemset(c->d_ctl, 0, CTL_N * sizeof(int)));
