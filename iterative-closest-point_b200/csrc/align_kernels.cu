@@ -700,6 +700,198 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
 }
 
 // ------------------------------------------------------------------------------------------------
+// Small clouds: the WHOLE find_corresponding loop (src/cpu.cc:55-79) in ONE cooperative launch.
+//
+// A cow-sized problem (2 903 x 2 903 points: 8.4 M pairs, ~1 us of FMA work) spends its time on kernel latencies: three
+// launches per iteration at 13-18 us each.  Here every block keeps the model's FP32 shadow in its shared memory for the
+// whole loop (it never changes), a WARP searches one scene point at a time, and an iteration is: search own points ->
+// moments of own points -> grid barrier -> every block adds the partials in the same fixed order and solves -> transform
+// own points + residual -> grid barrier -> every block adds the residual partials and takes the (identical)
+// convergence decision.  No scratch, no slots, no host round trip, no launch boundary inside the loop.
+//
+// Exactness is the tree search's argument without the tree (tree_kernels.cu "Why it is exact"): the FP32 surrogate
+// d2~ = fl(|p^ - m^_k|^2) of EVERY model point is evaluated (direct form on the c0-centred shadows); with u = 2^-24,
+// E = u (1+3u) (|p^| + Rm) and best2 = min_k d2~, any index attaining the reference's minimum satisfies
+//     d2~  <=  thr2 := ( sqrt(best2) (1+3u) + 2E )^2 (1+16u)          (all operations rounded up),
+// and every such point gets the reference's FP64 expression, merged by (value, lowest index).  Scene points with a
+// non-finite coordinate match index 0 and an overflowed surrogate (> 1e19 away) falls back to an FP64 scan, as everywhere.
+constexpr int SMALL_THREADS = 256;
+constexpr int SMALL_WARPS = SMALL_THREADS / 32;
+
+__device__ __forceinline__ float small_surrogate(float px, float py, float pz, const float4 m)
+{
+    const float dx = __fsub_rn(px, m.x), dy = __fsub_rn(py, m.y), dz = __fsub_rn(pz, m.z);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
+
+__device__ __forceinline__ double small_dist2_64(double px, double py, double pz, const Pt64* __restrict__ m64, int k)
+{
+    double mx, my, mz;
+    ld_pt64(m64, k, mx, my, mz);
+    const double dx = __dsub_rn(px, mx), dy = __dsub_rn(py, my), dz = __dsub_rn(pz, mz);
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+__global__ void __launch_bounds__(SMALL_THREADS, 2)
+icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
+                      double* __restrict__ p64x, double* __restrict__ p64y, double* __restrict__ p64z,
+                      float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz, int32_t* __restrict__ idx,
+                      int np, int np_pad, double* __restrict__ partials, double* __restrict__ mom, double* __restrict__ xf,
+                      double* __restrict__ err_sum, int* __restrict__ ctl, int max_iter, double n_global, double threshold,
+                      double* __restrict__ err_hist, int model0_nan)
+{
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) unsigned char small_smem[];
+    float4* sm = reinterpret_cast<float4*>(small_smem);                     // the model's FP32 shadow, nm entries
+    __shared__ double red[17 * SMALL_WARPS];
+    __shared__ double mom_s[MOM_N];
+    __shared__ double xf_s[XF_N];
+    __shared__ int s_k[SMALL_THREADS];                                      // matches of this block's points, by slot
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int nb = (int)gridDim.x;
+    const int n_warps = nb * SMALL_WARPS;
+    const int rounds = (np + n_warps - 1) / n_warps;                        // <= SMALL_THREADS / SMALL_WARPS (launcher)
+    const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
+    const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
+    const double DINF = __longlong_as_double(0x7ff0000000000000LL);
+    constexpr unsigned FULL = 0xffffffffu;
+    double* partials_err = partials + (size_t)nb * 17;
+
+    for (int k = threadIdx.x; k < nm; k += SMALL_THREADS) sm[k] = mhat[k];
+    __syncthreads();
+
+    // point slot t = r * SMALL_WARPS + w of this block  <->  scene point j = (blockIdx.x * SMALL_WARPS + w) + r * n_warps
+    const int my_r = threadIdx.x / SMALL_WARPS, my_w = threadIdx.x % SMALL_WARPS;
+    const int my_j = (blockIdx.x * SMALL_WARPS + my_w) + my_r * n_warps;    // the point this THREAD moves (phases M and T)
+    const bool my_valid = my_r < rounds && my_j < np;
+
+    for (int it = 0; it < max_iter; ++it) {
+        // ---- search: one warp per scene point ---------------------------------------------------------------
+        for (int r = 0; r < rounds; ++r) {
+            const int j = (blockIdx.x * SMALL_WARPS + w) + r * n_warps;
+            if (j >= np) break;                                             // warp-uniform
+            const float px = phx[j], py = phy[j], pz = phz[j];
+            const double qx = p64x[j], qy = p64y[j], qz = p64z[j];
+            int kbest = 0;
+            if (scene_point_finite(qx, qy, qz) && !model0_nan) {
+                float b2 = 3.4028235e38f;
+                for (int k = lane; k < nm; k += 32) b2 = fminf(b2, small_surrogate(px, py, pz, sm[k]));   // NaN: ignored
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) b2 = fminf(b2, __shfl_xor_sync(FULL, b2, o));
+                double v = DINF;
+                int kk = 0x7fffffff;
+                if (b2 < 3.4028235e38f) {
+                    const float H = __fsqrt_ru(__fmaf_ru(pz, pz, __fmaf_ru(py, py, __fmul_ru(px, px))));
+                    const float twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
+                    const float a = __fadd_ru(__fmul_ru(__fsqrt_ru(b2), 1.0000002f), twoE);
+                    const float thr2 = fminf(__fmul_ru(__fmul_ru(a, a), 1.000001f), 3.4028235e38f);
+                    for (int k = lane; k < nm; k += 32) {                   // ascending k per lane
+                        if (small_surrogate(px, py, pz, sm[k]) <= thr2) {
+                            const double vv = __dsqrt_rn(small_dist2_64(qx, qy, qz, m64, k));
+                            if (vv < v) { v = vv; kk = k; }
+                        }
+                    }
+                } else {                                                    // surrogate overflowed: plain FP64 scan
+                    for (int k = lane; k < nm; k += 32) {
+                        const double vv = __dsqrt_rn(small_dist2_64(qx, qy, qz, m64, k));
+                        if (vv < v) { v = vv; kk = k; }
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const double ov = __shfl_xor_sync(FULL, v, o);
+                    const int ok = __shfl_xor_sync(FULL, kk, o);
+                    if (ov < v || (ov == v && ok < kk)) { v = ov; kk = ok; }
+                }
+                kk = __shfl_sync(FULL, kk, 0);
+                kbest = kk == 0x7fffffff ? 0 : kk;                          // nothing accepted: every distance inf / NaN
+            }
+            if (lane == 0) { idx[j] = kbest; s_k[r * SMALL_WARPS + w] = kbest; }
+        }
+        __syncthreads();
+
+        // ---- K2: moments of this block's points (one thread per point) --------------------------------------
+        double acc[17];
+#pragma unroll
+        for (int i = 0; i < 17; ++i) acc[i] = 0.0;
+        double x = 0.0, y = 0.0, z = 0.0, bx = 0.0, by = 0.0, bz = 0.0;
+        if (my_valid) {
+            x = p64x[my_j]; y = p64y[my_j]; z = p64z[my_j];
+            ld_pt64(m64, s_k[threadIdx.x], bx, by, bz);
+            moments_accumulate(acc, x - c0x, y - c0y, z - c0z, bx - c0x, by - c0y, bz - c0z);
+        }
+        block_sum<17>(acc, red);
+        if (threadIdx.x == 0)
+#pragma unroll
+            for (int i = 0; i < 17; ++i) partials[(size_t)i * nb + blockIdx.x] = acc[i];
+        grid.sync();
+
+        // ---- K3: every block adds the partials in the same order and solves ---------------------------------
+        double tot[17];
+#pragma unroll
+        for (int i = 0; i < 17; ++i) tot[i] = 0.0;
+        for (int b = threadIdx.x; b < nb; b += SMALL_THREADS)
+#pragma unroll
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)i * nb + b]);
+        block_sum<17>(tot, red);
+        if (threadIdx.x == 0) {
+            mom_s[0] = (double)np;
+#pragma unroll
+            for (int i = 0; i < 17; ++i) mom_s[1 + i] = tot[i];
+            horn_solve(geo, mom_s, xf_s);
+            if (blockIdx.x == 0) {
+                for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];
+                for (int i = 0; i < MOM_N; ++i) mom[i] = mom_s[i];
+            }
+        }
+        __syncthreads();
+
+        // ---- K4: transform own points in place, residual (src/cpu.cc:29-40, same operation order) ----------
+        double e[1] = {0.0};
+        {
+            const double sc = xf_s[0];
+            double sr[9];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(sc, xf_s[1 + i]);
+            const double tx = xf_s[10], ty = xf_s[11], tz = xf_s[12];
+            float fx = 0.f, fy = 0.f, fz = 0.f;
+            if (my_valid) {
+                const double nx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
+                const double ny = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
+                const double nz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
+                const double ex = __dsub_rn(bx, nx), ey = __dsub_rn(by, ny), ez = __dsub_rn(bz, nz);
+                e[0] = __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
+                p64x[my_j] = nx; p64y[my_j] = ny; p64z[my_j] = nz;
+                fx = (float)(nx - c0x); fy = (float)(ny - c0y); fz = (float)(nz - c0z);
+                phx[my_j] = fx; phy[my_j] = fy; phz[my_j] = fz;
+                if (my_j == np - 1)                                         // padding of the FP32 shadow = the last point
+                    for (int q2 = np; q2 < np_pad; ++q2) { phx[q2] = fx; phy[q2] = fy; phz[q2] = fz; }
+            }
+        }
+        block_sum<1>(e, red);
+        if (threadIdx.x == 0) partials_err[blockIdx.x] = e[0];
+        grid.sync();
+
+        // ---- close the iteration: every block adds the residual partials in the same order ------------------
+        double te[1] = {0.0};
+        for (int b = threadIdx.x; b < nb; b += SMALL_THREADS) te[0] += __ldcg(&partials_err[b]);
+        block_sum<1>(te, red);
+        if (threadIdx.x == 0) red[0] = te[0];
+        __syncthreads();
+        const double total = red[0];
+        const double err = (total + total) / n_global;                      // src/cpu.cc:67-77
+        __syncthreads();                                                    // red[] is reused by the next block_sum
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            err_sum[0] = total;
+            err_hist[it] = err;
+            ctl[CTL_ITERS] = it + 1;
+            if (err < threshold) ctl[CTL_DONE] = 1;
+        }
+        if (err < threshold) break;                                         // identical in every block
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Preparation kernels (run once per icp_set_model / icp_set_scene, not per iteration).
 
 // Bounding box of an AoS FP64 cloud: out = min[3], max[3].  Block partials -> the last block (ticket) folds them.
@@ -1029,6 +1221,40 @@ void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_ou
 void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st)
 {
     centroid_export_kernel<<<1, 1, 0, st>>>(m.geo, mom, out6);
+}
+
+int small_loop_max_blocks(int sm_count, size_t smem_bytes)
+{
+    if (smem_bytes > 200 * 1024) return 0;
+    if (cudaFuncSetAttribute(icp_small_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, icp_small_loop_kernel, SMALL_THREADS, smem_bytes) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        return 0;
+    }
+    return per_sm * sm_count;
+}
+
+int small_loop_points_per_block() { return SMALL_THREADS; }
+
+int launch_small_loop(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, double* xf,
+                      double* err_sum, int* ctl, int max_iter, double n_global, double threshold, double* err_hist,
+                      int model0_nan, cudaStream_t st)
+{
+    const size_t smem = (size_t)m.nm * sizeof(float4);
+    const Pt64* a0 = m.m64;
+    const float4* a1 = m.mhat;
+    int nm = (int)m.nm, np = (int)s.np, np_pad = (int)s.np_pad;
+    const double* a3 = m.geo;
+    double *b0 = s.p64x, *b1 = s.p64y, *b2 = s.p64z;
+    float *f0 = s.phx, *f1 = s.phy, *f2 = s.phz;
+    int32_t* ix = s.idx;
+    void* args[] = {&a0, &a1, &nm, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum, &ctl,
+                    &max_iter, &n_global, &threshold, &err_hist, &model0_nan};
+    return (int)cudaLaunchCooperativeKernel((const void*)icp_small_loop_kernel, dim3(n_blocks), dim3(SMALL_THREADS), args, smem, st);
 }
 
 void launch_subtract_col(const double* M_aos, int64_t n, double mx, double my, double mz, double* out_aos,
