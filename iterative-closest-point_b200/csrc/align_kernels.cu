@@ -708,6 +708,10 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
 // moments of own points -> grid barrier -> every block adds the partials in the same fixed order and solves -> transform
 // own points + residual -> grid barrier -> every block adds the residual partials and takes the (identical)
 // convergence decision.  No scratch, no slots, no host round trip, no launch boundary inside the loop.
+// (Second version: the first one - one scene point per warp at a time, two grid barriers per iteration - took 44 us per
+// cow iteration, 43 % of it waiting at the barriers and the rest bound by shared-memory bandwidth; now a warp searches
+// four of its points per pass over the model, and the residual partials travel with the NEXT step's moment partials, so an
+// iteration has ONE grid barrier.)
 //
 // Exactness is the tree search's argument without the tree (tree_kernels.cu "Why it is exact"): the FP32 surrogate
 // d2~ = fl(|p^ - m^_k|^2) of EVERY model point is evaluated (direct form on the c0-centred shadows); with u = 2^-24,
@@ -732,6 +736,8 @@ __device__ __forceinline__ double small_dist2_64(double px, double py, double pz
     return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
+constexpr int SMALL_R = 4;      // scene points a warp searches at once (one LDS.128 of the model serves all of them)
+
 __global__ void __launch_bounds__(SMALL_THREADS, 2)
 icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
                       double* __restrict__ p64x, double* __restrict__ p64y, double* __restrict__ p64z,
@@ -743,9 +749,10 @@ icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ m
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char small_smem[];
     float4* sm = reinterpret_cast<float4*>(small_smem);                     // the model's FP32 shadow, nm entries
-    __shared__ double red[17 * SMALL_WARPS];
+    __shared__ double red[18 * SMALL_WARPS];
     __shared__ double mom_s[MOM_N];
     __shared__ double xf_s[XF_N];
+    __shared__ double s_e;                                                  // this block's residual partial of the last transform
     __shared__ int s_k[SMALL_THREADS];                                      // matches of this block's points, by slot
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int nb = (int)gridDim.x;
@@ -754,10 +761,11 @@ icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ m
     const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
     const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
     const double DINF = __longlong_as_double(0x7ff0000000000000LL);
+    const float FMAX = 3.4028235e38f;
     constexpr unsigned FULL = 0xffffffffu;
-    double* partials_err = partials + (size_t)nb * 17;
 
     for (int k = threadIdx.x; k < nm; k += SMALL_THREADS) sm[k] = mhat[k];
+    if (threadIdx.x == 0) s_e = 0.0;
     __syncthreads();
 
     // point slot t = r * SMALL_WARPS + w of this block  <->  scene point j = (blockIdx.x * SMALL_WARPS + w) + r * n_warps
@@ -765,79 +773,127 @@ icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ m
     const int my_j = (blockIdx.x * SMALL_WARPS + my_w) + my_r * n_warps;    // the point this THREAD moves (phases M and T)
     const bool my_valid = my_r < rounds && my_j < np;
 
-    for (int it = 0; it < max_iter; ++it) {
-        // ---- search: one warp per scene point ---------------------------------------------------------------
-        for (int r = 0; r < rounds; ++r) {
-            const int j = (blockIdx.x * SMALL_WARPS + w) + r * n_warps;
-            if (j >= np) break;                                             // warp-uniform
-            const float px = phx[j], py = phy[j], pz = phz[j];
-            const double qx = p64x[j], qy = p64y[j], qz = p64z[j];
-            int kbest = 0;
-            if (scene_point_finite(qx, qy, qz) && !model0_nan) {
-                float b2 = 3.4028235e38f;
-                for (int k = lane; k < nm; k += 32) b2 = fminf(b2, small_surrogate(px, py, pz, sm[k]));   // NaN: ignored
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) b2 = fminf(b2, __shfl_xor_sync(FULL, b2, o));
-                double v = DINF;
-                int kk = 0x7fffffff;
-                if (b2 < 3.4028235e38f) {
-                    const float H = __fsqrt_ru(__fmaf_ru(pz, pz, __fmaf_ru(py, py, __fmul_ru(px, px))));
-                    const float twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
-                    const float a = __fadd_ru(__fmul_ru(__fsqrt_ru(b2), 1.0000002f), twoE);
-                    const float thr2 = fminf(__fmul_ru(__fmul_ru(a, a), 1.000001f), 3.4028235e38f);
-                    for (int k = lane; k < nm; k += 32) {                   // ascending k per lane
-                        if (small_surrogate(px, py, pz, sm[k]) <= thr2) {
-                            const double vv = __dsqrt_rn(small_dist2_64(qx, qy, qz, m64, k));
-                            if (vv < v) { v = vv; kk = k; }
-                        }
-                    }
-                } else {                                                    // surrogate overflowed: plain FP64 scan
-                    for (int k = lane; k < nm; k += 32) {
-                        const double vv = __dsqrt_rn(small_dist2_64(qx, qy, qz, m64, k));
-                        if (vv < v) { v = vv; kk = k; }
-                    }
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    const double ov = __shfl_xor_sync(FULL, v, o);
-                    const int ok = __shfl_xor_sync(FULL, kk, o);
-                    if (ov < v || (ov == v && ok < kk)) { v = ov; kk = ok; }
-                }
-                kk = __shfl_sync(FULL, kk, 0);
-                kbest = kk == 0x7fffffff ? 0 : kk;                          // nothing accepted: every distance inf / NaN
-            }
-            if (lane == 0) { idx[j] = kbest; s_k[r * SMALL_WARPS + w] = kbest; }
-        }
-        __syncthreads();
-
-        // ---- K2: moments of this block's points (one thread per point) --------------------------------------
+    // Step `it` = search + moments of iteration `it`, ONE grid barrier, then: close iteration it - 1 (its residual
+    // partials travelled with this step's moment partials), solve and transform iteration `it`.  The convergence decision
+    // therefore lags the transform by one search; that search only fills s_k (the global idx[] is written after the
+    // decision), so on convergence everything is as the reference leaves it.  Step max_iter only closes the last iteration.
+    for (int it = 0; it <= max_iter; ++it) {
+        // With one barrier per step a fast block may already WRITE the next step's partials while a slow one still READS
+        // this step's: two buffers by step parity (a block cannot get two steps ahead: the barrier in between needs everyone).
+        double* pm = partials + (size_t)(it & 1) * 18 * nb;
+        double* partials_err = pm + (size_t)nb * 17;
         double acc[17];
 #pragma unroll
         for (int i = 0; i < 17; ++i) acc[i] = 0.0;
         double x = 0.0, y = 0.0, z = 0.0, bx = 0.0, by = 0.0, bz = 0.0;
-        if (my_valid) {
-            x = p64x[my_j]; y = p64y[my_j]; z = p64z[my_j];
-            ld_pt64(m64, s_k[threadIdx.x], bx, by, bz);
-            moments_accumulate(acc, x - c0x, y - c0y, z - c0z, bx - c0x, by - c0y, bz - c0z);
-        }
-        block_sum<17>(acc, red);
-        if (threadIdx.x == 0)
+        if (it < max_iter) {
+            // ---- search: a warp takes SMALL_R of its scene points at a time --------------------------------
+            for (int r0 = 0; r0 < rounds; r0 += SMALL_R) {
+                float px[SMALL_R], py[SMALL_R], pz[SMALL_R], b2[SMALL_R], thr2[SMALL_R];
+                double qx[SMALL_R], qy[SMALL_R], qz[SMALL_R], v[SMALL_R];
+                int kk[SMALL_R];
+                bool live[SMALL_R], ovf[SMALL_R];
 #pragma unroll
-            for (int i = 0; i < 17; ++i) partials[(size_t)i * nb + blockIdx.x] = acc[i];
+                for (int r = 0; r < SMALL_R; ++r) {
+                    const int j = (blockIdx.x * SMALL_WARPS + w) + (r0 + r) * n_warps;
+                    const bool in = r0 + r < rounds && j < np;
+                    const int jc = in ? j : 0;
+                    px[r] = phx[jc]; py[r] = phy[jc]; pz[r] = phz[jc];
+                    qx[r] = p64x[jc]; qy[r] = p64y[jc]; qz[r] = p64z[jc];
+                    live[r] = in && scene_point_finite(qx[r], qy[r], qz[r]) && !model0_nan;    // warp-uniform
+                    b2[r] = FMAX;
+                    v[r] = DINF;
+                    kk[r] = 0x7fffffff;
+                }
+                for (int k = lane; k < nm; k += 32) {                       // pass 1: the surrogate's minimum
+                    const float4 m = sm[k];
+#pragma unroll
+                    for (int r = 0; r < SMALL_R; ++r) b2[r] = fminf(b2[r], small_surrogate(px[r], py[r], pz[r], m));   // NaN: ignored
+                }
+#pragma unroll
+                for (int r = 0; r < SMALL_R; ++r) {
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) b2[r] = fminf(b2[r], __shfl_xor_sync(FULL, b2[r], o));
+                    ovf[r] = !(b2[r] < FMAX);                               // surrogate overflowed (> 1e19 away): FP64 scan below
+                    const float H = __fsqrt_ru(__fmaf_ru(pz[r], pz[r], __fmaf_ru(py[r], py[r], __fmul_ru(px[r], px[r]))));
+                    const float twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
+                    const float a = __fadd_ru(__fmul_ru(__fsqrt_ru(b2[r]), 1.0000002f), twoE);
+                    thr2[r] = (live[r] && !ovf[r]) ? fminf(__fmul_ru(__fmul_ru(a, a), 1.000001f), FMAX) : -1.0f;   // -1: nothing passes
+                }
+                for (int k = lane; k < nm; k += 32) {                       // pass 2: FP64 for everything within the threshold
+                    const float4 m = sm[k];
+#pragma unroll
+                    for (int r = 0; r < SMALL_R; ++r)
+                        if (small_surrogate(px[r], py[r], pz[r], m) <= thr2[r]) {
+                            const double vv = __dsqrt_rn(small_dist2_64(qx[r], qy[r], qz[r], m64, k));
+                            if (vv < v[r]) { v[r] = vv; kk[r] = k; }        // ascending k per lane: first minimum
+                        }
+                }
+#pragma unroll
+                for (int r = 0; r < SMALL_R; ++r) {
+                    if (live[r] && ovf[r])                                  // warp-uniform
+                        for (int k = lane; k < nm; k += 32) {
+                            const double vv = __dsqrt_rn(small_dist2_64(qx[r], qy[r], qz[r], m64, k));
+                            if (vv < v[r]) { v[r] = vv; kk[r] = k; }
+                        }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const double ov = __shfl_xor_sync(FULL, v[r], o);
+                        const int ok = __shfl_xor_sync(FULL, kk[r], o);
+                        if (ov < v[r] || (ov == v[r] && ok < kk[r])) { v[r] = ov; kk[r] = ok; }
+                    }
+                    const int kb = __shfl_sync(FULL, kk[r], 0);
+                    // not live (non-finite scene point, or model point 0 is NaN) or nothing accepted: index 0
+                    if (lane == 0 && r0 + r < rounds) s_k[(r0 + r) * SMALL_WARPS + w] = kb == 0x7fffffff ? 0 : kb;
+                }
+            }
+            __syncthreads();
+
+            // ---- K2: moments of this block's points (one thread per point) ----------------------------------
+            if (my_valid) {
+                x = p64x[my_j]; y = p64y[my_j]; z = p64z[my_j];
+                ld_pt64(m64, s_k[threadIdx.x], bx, by, bz);
+                moments_accumulate(acc, x - c0x, y - c0y, z - c0z, bx - c0x, by - c0y, bz - c0z);
+            }
+            block_sum<17>(acc, red);
+        }
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int i = 0; i < 17; ++i) pm[(size_t)i * nb + blockIdx.x] = acc[i];
+            partials_err[blockIdx.x] = s_e;                                 // residual of the previous transform
+        }
         grid.sync();
 
-        // ---- K3: every block adds the partials in the same order and solves ---------------------------------
-        double tot[17];
+        // ---- every block adds the partials in the same fixed order -------------------------------------------
+        double tot[18];
 #pragma unroll
-        for (int i = 0; i < 17; ++i) tot[i] = 0.0;
-        for (int b = threadIdx.x; b < nb; b += SMALL_THREADS)
+        for (int i = 0; i < 18; ++i) tot[i] = 0.0;
+        for (int b = threadIdx.x; b < nb; b += SMALL_THREADS) {
 #pragma unroll
-            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)i * nb + b]);
-        block_sum<17>(tot, red);
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&pm[(size_t)i * nb + b]);
+            tot[17] += __ldcg(&partials_err[b]);
+        }
+        block_sum<18>(tot, red);
         if (threadIdx.x == 0) {
             mom_s[0] = (double)np;
 #pragma unroll
             for (int i = 0; i < 17; ++i) mom_s[1 + i] = tot[i];
+            red[0] = tot[17];
+        }
+        __syncthreads();
+        // ---- close iteration it - 1 (src/cpu.cc:67-77: the two residual sums are the same expression) -----------
+        const double total = red[0];
+        const double err = (total + total) / n_global;
+        if (it > 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+            err_sum[0] = total;
+            err_hist[it - 1] = err;
+            ctl[CTL_ITERS] = it;
+            if (err < threshold) ctl[CTL_DONE] = 1;
+        }
+        if ((it > 0 && err < threshold) || it == max_iter) break;          // identical in every block
+
+        // ---- K3 + K4: solve, publish the matches, transform own points in place, residual -------------------
+        if (threadIdx.x == 0) {
             horn_solve(geo, mom_s, xf_s);
             if (blockIdx.x == 0) {
                 for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];
@@ -845,8 +901,6 @@ icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ m
             }
         }
         __syncthreads();
-
-        // ---- K4: transform own points in place, residual (src/cpu.cc:29-40, same operation order) ----------
         double e[1] = {0.0};
         {
             const double sc = xf_s[0];
@@ -854,40 +908,24 @@ icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ m
 #pragma unroll
             for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(sc, xf_s[1 + i]);
             const double tx = xf_s[10], ty = xf_s[11], tz = xf_s[12];
-            float fx = 0.f, fy = 0.f, fz = 0.f;
             if (my_valid) {
+                idx[my_j] = s_k[threadIdx.x];
                 const double nx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
                 const double ny = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
                 const double nz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
                 const double ex = __dsub_rn(bx, nx), ey = __dsub_rn(by, ny), ez = __dsub_rn(bz, nz);
                 e[0] = __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
                 p64x[my_j] = nx; p64y[my_j] = ny; p64z[my_j] = nz;
-                fx = (float)(nx - c0x); fy = (float)(ny - c0y); fz = (float)(nz - c0z);
+                const float fx = (float)(nx - c0x), fy = (float)(ny - c0y), fz = (float)(nz - c0z);
                 phx[my_j] = fx; phy[my_j] = fy; phz[my_j] = fz;
                 if (my_j == np - 1)                                         // padding of the FP32 shadow = the last point
                     for (int q2 = np; q2 < np_pad; ++q2) { phx[q2] = fx; phy[q2] = fy; phz[q2] = fz; }
             }
         }
         block_sum<1>(e, red);
-        if (threadIdx.x == 0) partials_err[blockIdx.x] = e[0];
-        grid.sync();
-
-        // ---- close the iteration: every block adds the residual partials in the same order ------------------
-        double te[1] = {0.0};
-        for (int b = threadIdx.x; b < nb; b += SMALL_THREADS) te[0] += __ldcg(&partials_err[b]);
-        block_sum<1>(te, red);
-        if (threadIdx.x == 0) red[0] = te[0];
+        if (threadIdx.x == 0) s_e = e[0];
+        // the next step's search reads only this block's own points (just written by this block's threads)
         __syncthreads();
-        const double total = red[0];
-        const double err = (total + total) / n_global;                      // src/cpu.cc:67-77
-        __syncthreads();                                                    // red[] is reused by the next block_sum
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            err_sum[0] = total;
-            err_hist[it] = err;
-            ctl[CTL_ITERS] = it + 1;
-            if (err < threshold) ctl[CTL_DONE] = 1;
-        }
-        if (err < threshold) break;                                         // identical in every block
     }
 }
 

@@ -400,7 +400,7 @@ int small_loop_blocks(icp_ctx* c)
     }
     int nb = (int)((c->s.np + 7) / 8);
     if (nb > c->small_blocks) nb = c->small_blocks;
-    if (nb > c->sm_count * 4) nb = c->sm_count * 4;                 // d_partials holds 18 doubles per block
+    if (nb > c->sm_count * 2) nb = c->sm_count * 2;                 // d_partials holds 2 x 18 doubles per block of this kernel
     if (nb < 1 || (int64_t)nb * small_loop_points_per_block() < c->s.np) return 0;
     return nb;
 }
