@@ -370,7 +370,7 @@ class Harness:
         filt_ms_per_launch = filt_ms / max(r["iters_total"], 1)
         achieved = 8.0 * len(m) * len(p_shard) / (max(filt_ms_per_launch, 1e-12) * 1e-3) / 1e12
         roofline = None
-        if self.args.nn != "tree" and filt_ms > 0:      # clouds small enough for the one-launch loop kernel have no filter launches
+        if self.args.nn != "tree" and filt_ms > 0:
             roofline = {"bound": "fp32", "kernel": "nn_filter_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                         "frac": achieved / peak, "peak_source": peak_src, "algorithmic_flops_per_eval": 8,
                         "evals_per_launch": len(m) * len(p_shard), "avg_launch_ms": filt_ms_per_launch,

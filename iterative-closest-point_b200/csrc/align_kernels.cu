@@ -700,236 +700,6 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
 }
 
 // ------------------------------------------------------------------------------------------------
-// Small clouds: the WHOLE find_corresponding loop (src/cpu.cc:55-79) in ONE cooperative launch.
-//
-// A cow-sized problem (2 903 x 2 903 points: 8.4 M pairs, ~1 us of FMA work) spends its time on kernel latencies: three
-// launches per iteration at 13-18 us each.  Here every block keeps the model's FP32 shadow in its shared memory for the
-// whole loop (it never changes), a WARP searches one scene point at a time, and an iteration is: search own points ->
-// moments of own points -> grid barrier -> every block adds the partials in the same fixed order and solves -> transform
-// own points + residual -> grid barrier -> every block adds the residual partials and takes the (identical)
-// convergence decision.  No scratch, no slots, no host round trip, no launch boundary inside the loop.
-// (Second version: the first one - one scene point per warp at a time, two grid barriers per iteration - took 44 us per
-// cow iteration, 43 % of it waiting at the barriers and the rest bound by shared-memory bandwidth; now a warp searches
-// four of its points per pass over the model, and the residual partials travel with the NEXT step's moment partials, so an
-// iteration has ONE grid barrier.)
-//
-// Exactness is the tree search's argument without the tree (tree_kernels.cu "Why it is exact"): the FP32 surrogate
-// d2~ = fl(|p^ - m^_k|^2) of EVERY model point is evaluated (direct form on the c0-centred shadows); with u = 2^-24,
-// E = u (1+3u) (|p^| + Rm) and best2 = min_k d2~, any index attaining the reference's minimum satisfies
-//     d2~  <=  thr2 := ( sqrt(best2) (1+3u) + 2E )^2 (1+16u)          (all operations rounded up),
-// and every such point gets the reference's FP64 expression, merged by (value, lowest index).  Scene points with a
-// non-finite coordinate match index 0 and an overflowed surrogate (> 1e19 away) falls back to an FP64 scan, as everywhere.
-constexpr int SMALL_THREADS = 256;
-constexpr int SMALL_WARPS = SMALL_THREADS / 32;
-
-__device__ __forceinline__ float small_surrogate(float px, float py, float pz, const float4 m)
-{
-    const float dx = __fsub_rn(px, m.x), dy = __fsub_rn(py, m.y), dz = __fsub_rn(pz, m.z);
-    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
-}
-
-__device__ __forceinline__ double small_dist2_64(double px, double py, double pz, const Pt64* __restrict__ m64, int k)
-{
-    double mx, my, mz;
-    ld_pt64(m64, k, mx, my, mz);
-    const double dx = __dsub_rn(px, mx), dy = __dsub_rn(py, my), dz = __dsub_rn(pz, mz);
-    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-}
-
-constexpr int SMALL_R = 4;      // scene points a warp searches at once (one LDS.128 of the model serves all of them)
-
-__global__ void __launch_bounds__(SMALL_THREADS, 2)
-icp_small_loop_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, int nm, const double* __restrict__ geo,
-                      double* __restrict__ p64x, double* __restrict__ p64y, double* __restrict__ p64z,
-                      float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz, int32_t* __restrict__ idx,
-                      int np, int np_pad, double* __restrict__ partials, double* __restrict__ mom, double* __restrict__ xf,
-                      double* __restrict__ err_sum, int* __restrict__ ctl, int max_iter, double n_global, double threshold,
-                      double* __restrict__ err_hist, int model0_nan)
-{
-    cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) unsigned char small_smem[];
-    float4* sm = reinterpret_cast<float4*>(small_smem);                     // the model's FP32 shadow, nm entries
-    __shared__ double red[18 * SMALL_WARPS];
-    __shared__ double mom_s[MOM_N];
-    __shared__ double xf_s[XF_N];
-    __shared__ double s_e;                                                  // this block's residual partial of the last transform
-    __shared__ int s_k[SMALL_THREADS];                                      // matches of this block's points, by slot
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int nb = (int)gridDim.x;
-    const int n_warps = nb * SMALL_WARPS;
-    const int rounds = (np + n_warps - 1) / n_warps;                        // <= SMALL_THREADS / SMALL_WARPS (launcher)
-    const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
-    const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
-    const double DINF = __longlong_as_double(0x7ff0000000000000LL);
-    const float FMAX = 3.4028235e38f;
-    constexpr unsigned FULL = 0xffffffffu;
-
-    for (int k = threadIdx.x; k < nm; k += SMALL_THREADS) sm[k] = mhat[k];
-    if (threadIdx.x == 0) s_e = 0.0;
-    __syncthreads();
-
-    // point slot t = r * SMALL_WARPS + w of this block  <->  scene point j = (blockIdx.x * SMALL_WARPS + w) + r * n_warps
-    const int my_r = threadIdx.x / SMALL_WARPS, my_w = threadIdx.x % SMALL_WARPS;
-    const int my_j = (blockIdx.x * SMALL_WARPS + my_w) + my_r * n_warps;    // the point this THREAD moves (phases M and T)
-    const bool my_valid = my_r < rounds && my_j < np;
-
-    // Step `it` = search + moments of iteration `it`, ONE grid barrier, then: close iteration it - 1 (its residual
-    // partials travelled with this step's moment partials), solve and transform iteration `it`.  The convergence decision
-    // therefore lags the transform by one search; that search only fills s_k (the global idx[] is written after the
-    // decision), so on convergence everything is as the reference leaves it.  Step max_iter only closes the last iteration.
-    for (int it = 0; it <= max_iter; ++it) {
-        // With one barrier per step a fast block may already WRITE the next step's partials while a slow one still READS
-        // this step's: two buffers by step parity (a block cannot get two steps ahead: the barrier in between needs everyone).
-        double* pm = partials + (size_t)(it & 1) * 18 * nb;
-        double* partials_err = pm + (size_t)nb * 17;
-        double acc[17];
-#pragma unroll
-        for (int i = 0; i < 17; ++i) acc[i] = 0.0;
-        double x = 0.0, y = 0.0, z = 0.0, bx = 0.0, by = 0.0, bz = 0.0;
-        if (it < max_iter) {
-            // ---- search: a warp takes SMALL_R of its scene points at a time --------------------------------
-            for (int r0 = 0; r0 < rounds; r0 += SMALL_R) {
-                float px[SMALL_R], py[SMALL_R], pz[SMALL_R], b2[SMALL_R], thr2[SMALL_R];
-                double qx[SMALL_R], qy[SMALL_R], qz[SMALL_R], v[SMALL_R];
-                int kk[SMALL_R];
-                bool live[SMALL_R], ovf[SMALL_R];
-#pragma unroll
-                for (int r = 0; r < SMALL_R; ++r) {
-                    const int j = (blockIdx.x * SMALL_WARPS + w) + (r0 + r) * n_warps;
-                    const bool in = r0 + r < rounds && j < np;
-                    const int jc = in ? j : 0;
-                    px[r] = phx[jc]; py[r] = phy[jc]; pz[r] = phz[jc];
-                    qx[r] = p64x[jc]; qy[r] = p64y[jc]; qz[r] = p64z[jc];
-                    live[r] = in && scene_point_finite(qx[r], qy[r], qz[r]) && !model0_nan;    // warp-uniform
-                    b2[r] = FMAX;
-                    v[r] = DINF;
-                    kk[r] = 0x7fffffff;
-                }
-                for (int k = lane; k < nm; k += 32) {                       // pass 1: the surrogate's minimum
-                    const float4 m = sm[k];
-#pragma unroll
-                    for (int r = 0; r < SMALL_R; ++r) b2[r] = fminf(b2[r], small_surrogate(px[r], py[r], pz[r], m));   // NaN: ignored
-                }
-#pragma unroll
-                for (int r = 0; r < SMALL_R; ++r) {
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) b2[r] = fminf(b2[r], __shfl_xor_sync(FULL, b2[r], o));
-                    ovf[r] = !(b2[r] < FMAX);                               // surrogate overflowed (> 1e19 away): FP64 scan below
-                    const float H = __fsqrt_ru(__fmaf_ru(pz[r], pz[r], __fmaf_ru(py[r], py[r], __fmul_ru(px[r], px[r]))));
-                    const float twoE = __fadd_ru(__fmul_ru(1.1920932e-7f /* > 2^-23 (1+3u) */, __fadd_ru(H, Rm)), 1.0e-30f);
-                    const float a = __fadd_ru(__fmul_ru(__fsqrt_ru(b2[r]), 1.0000002f), twoE);
-                    thr2[r] = (live[r] && !ovf[r]) ? fminf(__fmul_ru(__fmul_ru(a, a), 1.000001f), FMAX) : -1.0f;   // -1: nothing passes
-                }
-                for (int k = lane; k < nm; k += 32) {                       // pass 2: FP64 for everything within the threshold
-                    const float4 m = sm[k];
-#pragma unroll
-                    for (int r = 0; r < SMALL_R; ++r)
-                        if (small_surrogate(px[r], py[r], pz[r], m) <= thr2[r]) {
-                            const double vv = __dsqrt_rn(small_dist2_64(qx[r], qy[r], qz[r], m64, k));
-                            if (vv < v[r]) { v[r] = vv; kk[r] = k; }        // ascending k per lane: first minimum
-                        }
-                }
-#pragma unroll
-                for (int r = 0; r < SMALL_R; ++r) {
-                    if (live[r] && ovf[r])                                  // warp-uniform
-                        for (int k = lane; k < nm; k += 32) {
-                            const double vv = __dsqrt_rn(small_dist2_64(qx[r], qy[r], qz[r], m64, k));
-                            if (vv < v[r]) { v[r] = vv; kk[r] = k; }
-                        }
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) {
-                        const double ov = __shfl_xor_sync(FULL, v[r], o);
-                        const int ok = __shfl_xor_sync(FULL, kk[r], o);
-                        if (ov < v[r] || (ov == v[r] && ok < kk[r])) { v[r] = ov; kk[r] = ok; }
-                    }
-                    const int kb = __shfl_sync(FULL, kk[r], 0);
-                    // not live (non-finite scene point, or model point 0 is NaN) or nothing accepted: index 0
-                    if (lane == 0 && r0 + r < rounds) s_k[(r0 + r) * SMALL_WARPS + w] = kb == 0x7fffffff ? 0 : kb;
-                }
-            }
-            __syncthreads();
-
-            // ---- K2: moments of this block's points (one thread per point) ----------------------------------
-            if (my_valid) {
-                x = p64x[my_j]; y = p64y[my_j]; z = p64z[my_j];
-                ld_pt64(m64, s_k[threadIdx.x], bx, by, bz);
-                moments_accumulate(acc, x - c0x, y - c0y, z - c0z, bx - c0x, by - c0y, bz - c0z);
-            }
-            block_sum<17>(acc, red);
-        }
-        if (threadIdx.x == 0) {
-#pragma unroll
-            for (int i = 0; i < 17; ++i) pm[(size_t)i * nb + blockIdx.x] = acc[i];
-            partials_err[blockIdx.x] = s_e;                                 // residual of the previous transform
-        }
-        grid.sync();
-
-        // ---- every block adds the partials in the same fixed order -------------------------------------------
-        double tot[18];
-#pragma unroll
-        for (int i = 0; i < 18; ++i) tot[i] = 0.0;
-        for (int b = threadIdx.x; b < nb; b += SMALL_THREADS) {
-#pragma unroll
-            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&pm[(size_t)i * nb + b]);
-            tot[17] += __ldcg(&partials_err[b]);
-        }
-        block_sum<18>(tot, red);
-        if (threadIdx.x == 0) {
-            mom_s[0] = (double)np;
-#pragma unroll
-            for (int i = 0; i < 17; ++i) mom_s[1 + i] = tot[i];
-            red[0] = tot[17];
-        }
-        __syncthreads();
-        // ---- close iteration it - 1 (src/cpu.cc:67-77: the two residual sums are the same expression) -----------
-        const double total = red[0];
-        const double err = (total + total) / n_global;
-        if (it > 0 && blockIdx.x == 0 && threadIdx.x == 0) {
-            err_sum[0] = total;
-            err_hist[it - 1] = err;
-            ctl[CTL_ITERS] = it;
-            if (err < threshold) ctl[CTL_DONE] = 1;
-        }
-        if ((it > 0 && err < threshold) || it == max_iter) break;          // identical in every block
-
-        // ---- K3 + K4: solve, publish the matches, transform own points in place, residual -------------------
-        if (threadIdx.x == 0) {
-            horn_solve(geo, mom_s, xf_s);
-            if (blockIdx.x == 0) {
-                for (int i = 0; i < XF_N; ++i) xf[i] = xf_s[i];
-                for (int i = 0; i < MOM_N; ++i) mom[i] = mom_s[i];
-            }
-        }
-        __syncthreads();
-        double e[1] = {0.0};
-        {
-            const double sc = xf_s[0];
-            double sr[9];
-#pragma unroll
-            for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(sc, xf_s[1 + i]);
-            const double tx = xf_s[10], ty = xf_s[11], tz = xf_s[12];
-            if (my_valid) {
-                idx[my_j] = s_k[threadIdx.x];
-                const double nx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[0], x), __dmul_rn(sr[1], y)), __dmul_rn(sr[2], z)), tx);
-                const double ny = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[3], x), __dmul_rn(sr[4], y)), __dmul_rn(sr[5], z)), ty);
-                const double nz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(sr[6], x), __dmul_rn(sr[7], y)), __dmul_rn(sr[8], z)), tz);
-                const double ex = __dsub_rn(bx, nx), ey = __dsub_rn(by, ny), ez = __dsub_rn(bz, nz);
-                e[0] = __dadd_rn(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)), __dmul_rn(ez, ez));
-                p64x[my_j] = nx; p64y[my_j] = ny; p64z[my_j] = nz;
-                const float fx = (float)(nx - c0x), fy = (float)(ny - c0y), fz = (float)(nz - c0z);
-                phx[my_j] = fx; phy[my_j] = fy; phz[my_j] = fz;
-                if (my_j == np - 1)                                         // padding of the FP32 shadow = the last point
-                    for (int q2 = np; q2 < np_pad; ++q2) { phx[q2] = fx; phy[q2] = fy; phz[q2] = fz; }
-            }
-        }
-        block_sum<1>(e, red);
-        if (threadIdx.x == 0) s_e = e[0];
-        // the next step's search reads only this block's own points (just written by this block's threads)
-        __syncthreads();
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
 // Preparation kernels (run once per icp_set_model / icp_set_scene, not per iteration).
 
 // Bounding box of an AoS FP64 cloud: out = min[3], max[3].  Block partials -> the last block (ticket) folds them.
@@ -1259,40 +1029,6 @@ void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_ou
 void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st)
 {
     centroid_export_kernel<<<1, 1, 0, st>>>(m.geo, mom, out6);
-}
-
-int small_loop_max_blocks(int sm_count, size_t smem_bytes)
-{
-    if (smem_bytes > 200 * 1024) return 0;
-    if (cudaFuncSetAttribute(icp_small_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes) != cudaSuccess) {
-        cudaGetLastError();
-        return 0;
-    }
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, icp_small_loop_kernel, SMALL_THREADS, smem_bytes) != cudaSuccess || per_sm < 1) {
-        cudaGetLastError();
-        return 0;
-    }
-    return per_sm * sm_count;
-}
-
-int small_loop_points_per_block() { return SMALL_THREADS; }
-
-int launch_small_loop(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, double* xf,
-                      double* err_sum, int* ctl, int max_iter, double n_global, double threshold, double* err_hist,
-                      int model0_nan, cudaStream_t st)
-{
-    const size_t smem = (size_t)m.nm * sizeof(float4);
-    const Pt64* a0 = m.m64;
-    const float4* a1 = m.mhat;
-    int nm = (int)m.nm, np = (int)s.np, np_pad = (int)s.np_pad;
-    const double* a3 = m.geo;
-    double *b0 = s.p64x, *b1 = s.p64y, *b2 = s.p64z;
-    float *f0 = s.phx, *f1 = s.phy, *f2 = s.phz;
-    int32_t* ix = s.idx;
-    void* args[] = {&a0, &a1, &nm, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum, &ctl,
-                    &max_iter, &n_global, &threshold, &err_hist, &model0_nan};
-    return (int)cudaLaunchCooperativeKernel((const void*)icp_small_loop_kernel, dim3(n_blocks), dim3(SMALL_THREADS), args, smem, st);
 }
 
 void launch_subtract_col(const double* M_aos, int64_t n, double mx, double my, double mz, double* out_aos,

@@ -112,8 +112,6 @@ struct icp_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> ev_filter;
     nccl_comm comm = nullptr; int rank = 0, world = 1;
-    int small_mode = 0;                    // ICP_SMALL: 0 auto (whole-loop kernel for small clouds), 1 never
-    int small_blocks = 0, small_nm = -1;   // co-resident blocks of the whole-loop kernel for a model of small_nm points
     int exact_mode = 0;                    // ICP_EXACT: 0 auto, 1 always inside nn_refine, 2 always the nn_exact kernel
     bool model0_nan = false;               // model point 0 has a NaN coordinate: the reference's first-minimum scan never leaves it
     size_t cap_nm = 0, cap_np = 0;         // allocated capacities (points): buffers only ever grow
@@ -385,26 +383,6 @@ int align_step(icp_ctx* c, int honor_done, int in_place, int finish, double n_gl
     return launched;
 }
 
-// Small clouds run the whole loop in one cooperative launch (icp_small_loop_kernel, align_kernels.cu): brute-force search
-// mode, one GPU, nothing else sharing it, the model's FP32 shadow fits a block's shared memory and FP32 squares of the
-// centred coordinates stay in the normal range.  Returns the grid size, 0 = take the per-kernel loop.
-constexpr int64_t SMALL_MAX_NM = 8192, SMALL_MAX_NP = 8192;
-int small_loop_blocks(icp_ctx* c)
-{
-    if (c->small_mode || c->nn_mode != ICP_NN_BRUTE || c->comm || c->in_group || c->is_lane || c->profile) return 0;
-    if (c->m.nm > SMALL_MAX_NM || c->s.np > SMALL_MAX_NP) return 0;
-    if (!(c->h_Rm == 0.0 || (c->h_Rm >= 1e-12 && c->h_Rm <= 1e12))) return 0;
-    if (c->small_nm != (int)c->m.nm) {
-        c->small_blocks = small_loop_max_blocks(c->sm_count, (size_t)c->m.nm * sizeof(float4));
-        c->small_nm = (int)c->m.nm;
-    }
-    int nb = (int)((c->s.np + 7) / 8);
-    if (nb > c->small_blocks) nb = c->small_blocks;
-    if (nb > c->sm_count * 2) nb = c->sm_count * 2;                 // d_partials holds 2 x 18 doubles per block of this kernel
-    if (nb < 1 || (int64_t)nb * small_loop_points_per_block() < c->s.np) return 0;
-    return nb;
-}
-
 int reset_ctl(icp_ctx* c)
 {
     CK(cudaMemsetAsync(c->d_ctl, 0, CTL_N * sizeof(int), c->st));
@@ -462,7 +440,6 @@ static int create_body(icp_ctx* c, int device)
     if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
     if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
     if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
-    if (const char* e = getenv("ICP_SMALL")) c->small_mode = !strcmp(e, "0") || !strcmp(e, "off") ? 1 : 0;
     if (const char* e = getenv("ICP_EXACT")) c->exact_mode = !strcmp(e, "inline") ? 1 : (!strcmp(e, "kernel") ? 2 : 0);
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
@@ -811,14 +788,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     const int LA = (c->lookahead > 0 && !nccl_path(c)) ? (c->lookahead < 2 ? 2 : c->lookahead) : 0;   // >= 2: see nn_filter_kernel
     *(volatile int*)c->h_progress = 0;
     c->progress_arg = LA ? c->d_progress : nullptr;
-    const int small_nb = small_loop_blocks(c);
-    if (small_nb > 0) {      // the whole loop in one cooperative launch
-        const int e = launch_small_loop(c->m, c->s, c->d_partials, small_nb, c->d_mom, c->d_xf, c->d_err_sum, c->d_ctl, max_iter,
-                                        np_glob, threshold, c->d_err_hist, c->model0_nan ? 1 : 0, c->st);
-        if (e != 0) { g_err = std::string("icp_small_loop launch: ") + cudaGetErrorString((cudaError_t)e); return ICP_ERR_CUDA; }
-        c->stats.kernels_launched = 1;
-    }
-    for (int it = 0; it < max_iter && small_nb == 0; ++it) {
+    for (int it = 0; it < max_iter; ++it) {
         if (LA && it >= LA) {
             const int w = wait_progress(c, it + 1 - LA, it);
             if (w < 0) return w;
@@ -864,7 +834,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
     c->stats.rerank_chunk += (int64_t)iters * c->s.np - ctl[CTL_AMB_TOTAL];
     cudaEventElapsedTime(&c->stats.ms_total, c->ev0, c->ev1);
     float f = 0.f, f_ref = 0.f, f_ex = 0.f, f_al = 0.f;
-    for (int it = 0; it < iters && small_nb == 0; ++it) {
+    for (int it = 0; it < iters; ++it) {
         cudaEvent_t* ev = &c->ev_filter[(size_t)EV * it];
         float ms = 0.f;
         cudaEventElapsedTime(&ms, ev[0], ev[1]);

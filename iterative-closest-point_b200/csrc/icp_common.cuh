@@ -168,14 +168,6 @@ int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, i
                        double threshold, double* err_hist, const PeerComm* peer, unsigned long long* trace,
                        cudaStream_t st);
 int align_fused_max_blocks(int sm_count);
-// Small clouds: the whole find_corresponding loop in ONE cooperative launch (the model's FP32 shadow lives in every block's
-// shared memory; a warp searches one scene point at a time).  small_loop_max_blocks: co-resident blocks for a model of
-// smem_bytes (0 = does not fit).  A block moves at most small_loop_points_per_block() scene points.
-int small_loop_max_blocks(int sm_count, size_t smem_bytes);
-int small_loop_points_per_block();
-int launch_small_loop(const ModelDev& m, const SceneDev& s, double* partials, int n_blocks, double* mom, double* xf,
-                      double* err_sum, int* ctl, int max_iter, double n_global, double threshold, double* err_hist,
-                      int model0_nan, cudaStream_t st);
 void launch_finish(const double* err_sum, double n_global, double threshold, double* err_hist, int* ctl,
                    cudaStream_t st);
 

@@ -16,7 +16,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def test_peer_mailbox_self_exchange(clouds, monkeypatch, align):
     import icp_b200
     monkeypatch.setenv("ICP_ALIGN", align)
-    monkeypatch.setenv("ICP_SMALL", "0")     # bit-identity is between the two per-kernel loops (the one-launch loop kernel sums in another order)
     m, p = clouds("cow_ref"), clouds("cow_tr1")
     plain = icp_b200.Context(0)
     plain.set_model(m)
@@ -60,7 +59,7 @@ def test_two_gpu_sharded_parity(nn):
 def test_group_of_one_device_is_a_plain_context(clouds):
     import icp_b200
     m, p = clouds("cow_ref"), clouds("cow_tr1")
-    plain = icp_b200.Context(0)              # both take the one-launch loop kernel (a group of one is a plain context)
+    plain = icp_b200.Context(0)
     plain.set_model(m)
     plain.set_scene(p)
     it0, hist0 = plain.run(30)
