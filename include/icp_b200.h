@@ -229,6 +229,20 @@ int icp_batch_run_multi(const int* devices, int ndev, int lanes, int64_t n_pairs
                         const int64_t* nm, const double* const* p_xyz, const int64_t* np, int max_iter, double threshold,
                         int check_sizes, int32_t* iters_out, double* err_out, double* const* new_p_out, double* srt_out);
 
+/* ---- no-allocation entry point -------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * icp_find_alignment_noalloc = the fused moments + Horn solve (K2 + K3; the s, R, t of icp_find_alignment_host, without
+ * its residual) on PAIRED clouds that already live in device memory: d_y_xyz[j] <-> d_p_xyz[j], n x 3 FP64 each, on
+ * the CURRENT device.  d_out20 (device, 20 doubles) receives s, R[9] row-major, t[3], mu_p[3], mu_y[3], 0.  The work is
+ * enqueued on `cuda_stream` (a cudaStream_t; NULL = the default stream) and the call returns without synchronising.
+ * It calls no cudaMalloc / cudaFree / allocating routine and needs no icp_ctx: the kernel's scratch (block partials and a
+ * ticket) is ONE file-scope device array of 80 768 bytes that every GPU loading the library holds until the process
+ * exits.  Limits and sharing: n <= 4 194 304 point pairs (ICP_ERR_INVALID beyond, with a message); all calls on a device
+ * share the array, so calls that overlap on the GPU (different streams, or several host threads) RACE - serialise them.
+ * The very first call on a device resolves the array's address (cudaGetSymbolAddress): make it outside a stream capture. */
+int icp_find_alignment_noalloc(const double* d_y_xyz, const double* d_p_xyz, int64_t n, double* d_out20, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

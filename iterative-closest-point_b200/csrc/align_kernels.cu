@@ -907,6 +907,65 @@ __global__ void subtract_col_kernel(const double* __restrict__ M, int64_t n, dou
     out[3 * i] = M[3 * i] - mx; out[3 * i + 1] = M[3 * i + 1] - my; out[3 * i + 2] = M[3 * i + 2] - mz;
 }
 
+// ------------------------------------------------------------------------------------------------
+// No-allocation variant of K2 + K3 (icp_find_alignment_noalloc, see the end of this file).  No counterpart in the
+// reference; added for callers that cannot call cudaMalloc.
+// Same maths as moments_kernel + horn_solve on PAIRED clouds given as AoS FP64 device arrays (p_j <-> y_j); the block
+// partials and the ticket live in a file-scope device array instead of a context's cudaMalloc'ed scratch.
+constexpr int NOALLOC_MAX_BLOCKS = 592;                       // 4 CTAs x 148 SMs
+constexpr long long NOALLOC_MAX_POINTS = 1ll << 22;           // stated maximum of the entry point: 4 194 304 pairs
+constexpr int NOALLOC_SCRATCH_DOUBLES = NOALLOC_MAX_BLOCKS * 17 + 32;      // partials [blocks][17] + a 256-byte tail (ticket)
+// 80 768 bytes, held by every GPU that loads the library until the process exits.  In HOST code this name is a host-side
+// stand-in, not a device address: the address comes from cudaGetSymbolAddress (noalloc_scratch_ptr below).
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SCRATCH_DOUBLES];
+
+__global__ void __launch_bounds__(RED_THREADS, 4)
+moments_pairs_noalloc_kernel(const double* __restrict__ p_aos, const double* __restrict__ y_aos, int n,
+                             double* __restrict__ scratch, double* __restrict__ out_xf)
+{
+    __shared__ double red[17 * (RED_THREADS / 32)];
+    __shared__ double mom_s[MOM_N];
+    __shared__ double geo_s[4];
+    __shared__ int is_last;
+    double* partials = scratch;
+    int* ticket = reinterpret_cast<int*>(scratch + NOALLOC_MAX_BLOCKS * 17);
+    // pivot of the sums: the first y point (any point near the clouds keeps the algebraic centring harmless)
+    const double c0x = y_aos[0], c0y = y_aos[1], c0z = y_aos[2];
+    double acc[17];
+#pragma unroll
+    for (int i = 0; i < 17; ++i) acc[i] = 0.0;
+    for (int j = blockIdx.x * RED_THREADS + threadIdx.x; j < n; j += gridDim.x * RED_THREADS)
+        moments_accumulate(acc, p_aos[3 * (size_t)j] - c0x, p_aos[3 * (size_t)j + 1] - c0y, p_aos[3 * (size_t)j + 2] - c0z,
+                           y_aos[3 * (size_t)j] - c0x, y_aos[3 * (size_t)j + 1] - c0y, y_aos[3 * (size_t)j + 2] - c0z);
+    block_sum<17>(acc, red);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < 17; ++i) partials[(size_t)blockIdx.x * 17 + i] = acc[i];
+        __threadfence();
+        is_last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double tot[17];
+#pragma unroll
+        for (int i = 0; i < 17; ++i) tot[i] = 0.0;
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS)
+#pragma unroll
+            for (int i = 0; i < 17; ++i) tot[i] += __ldcg(&partials[(size_t)b * 17 + i]);
+        block_sum<17>(tot, red);
+        if (threadIdx.x == 0) {
+            mom_s[0] = (double)n;
+#pragma unroll
+            for (int i = 0; i < 17; ++i) mom_s[1 + i] = tot[i];
+            geo_s[0] = c0x; geo_s[1] = c0y; geo_s[2] = c0z; geo_s[3] = 0.0;
+            horn_solve(geo_s, mom_s, out_xf);          // s, R[9], t[3], mu_p[3], mu_y[3] (src/cpu.cc:113-167)
+            out_xf[19] = 0.0;
+            *ticket = 0;                               // the next call starts from zero (it clears the ticket again anyway)
+        }
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
@@ -1038,3 +1097,75 @@ void launch_subtract_col(const double* M_aos, int64_t n, double mx, double my, d
 }
 
 }  // namespace icpb
+
+// ------------------------------------------------------------------------------------------------
+// icp_find_alignment_noalloc (include/icp_b200.h): K2 + K3 on paired device clouds without any allocation.
+#include <mutex>
+#include <string>
+
+#include "../../include/icp_b200.h"
+
+namespace icpb {
+void set_last_error(const std::string& msg);      // icp_api.cu: what icp_last_error() returns on the calling thread
+}
+
+namespace {
+// Device address of g_noalloc_scratch on the CURRENT device; resolved once per device, with that device current.
+int noalloc_scratch_ptr(double** out)
+{
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static double* ptr[MAX_DEV] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        icpb::set_last_error(std::string("icp_find_alignment_noalloc: no current CUDA device (") + cudaGetErrorString(e) + ")");
+        cudaGetLastError();
+        return ICP_ERR_NO_DEVICE;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[dev]) {
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, icpb::g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            icpb::set_last_error(std::string("icp_find_alignment_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+            cudaGetLastError();
+            return ICP_ERR_CUDA;
+        }
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return ICP_OK;
+}
+}  // namespace
+
+extern "C" int icp_find_alignment_noalloc(const double* d_y_xyz, const double* d_p_xyz, int64_t n, double* d_out20,
+                                          void* cuda_stream)
+{
+    if (!d_y_xyz || !d_p_xyz || !d_out20 || n < 1) {
+        icpb::set_last_error("icp_find_alignment_noalloc: bad arguments (device pointers y, p, out and n >= 1 required)");
+        return ICP_ERR_INVALID;
+    }
+    if (n > icpb::NOALLOC_MAX_POINTS) {
+        icpb::set_last_error("icp_find_alignment_noalloc: n = " + std::to_string((long long)n) + " exceeds the maximum of " +
+                             std::to_string(icpb::NOALLOC_MAX_POINTS) + " point pairs of the no-allocation entry point (use icp_find_alignment)");
+        return ICP_ERR_INVALID;
+    }
+    double* scratch = nullptr;
+    const int r = noalloc_scratch_ptr(&scratch);
+    if (r) return r;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    // the ticket must start at zero whatever an earlier (possibly aborted) call left in the shared array
+    cudaError_t e = cudaMemsetAsync(scratch + icpb::NOALLOC_MAX_BLOCKS * 17, 0, 256, st);
+    if (e == cudaSuccess) {
+        int64_t blocks = (n + icpb::RED_THREADS - 1) / icpb::RED_THREADS;
+        if (blocks > icpb::NOALLOC_MAX_BLOCKS) blocks = icpb::NOALLOC_MAX_BLOCKS;
+        icpb::moments_pairs_noalloc_kernel<<<(int)blocks, icpb::RED_THREADS, 0, st>>>(d_p_xyz, d_y_xyz, (int)n, scratch, d_out20);
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) {
+        icpb::set_last_error(std::string("icp_find_alignment_noalloc: ") + cudaGetErrorString(e));
+        return ICP_ERR_CUDA;
+    }
+    return ICP_OK;
+}

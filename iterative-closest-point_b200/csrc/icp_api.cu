@@ -84,6 +84,11 @@ NcclApi g_nccl;
 }  // namespace
 
 
+namespace icpb {
+// lets the other translation units of the library report through icp_last_error()
+void set_last_error(const std::string& msg) { g_err = msg; }
+}  // namespace icpb
+
 constexpr int TRACE_WORDS = 16 + 5 * 32;   // block 0's phase stamps + (SM id, entry, barrier, solve, exit) of the first 32 blocks
 
 struct icp_ctx {

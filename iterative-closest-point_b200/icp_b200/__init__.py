@@ -36,7 +36,7 @@ EXPORTS = [
     "icp_group_create", "icp_group_destroy", "icp_group_size", "icp_group_member", "icp_group_set_model", "icp_group_set_scene",
     "icp_group_reset_scene", "icp_group_set_nn_mode", "icp_group_closest", "icp_group_centroid", "icp_group_find_alignment",
     "icp_group_err_compute", "icp_group_run", "icp_group_get_scene", "icp_group_get_indices", "icp_group_get_transform",
-    "icp_group_get_stats", "icp_batch_run_multi",
+    "icp_group_get_stats", "icp_batch_run_multi", "icp_find_alignment_noalloc",
 ]
 
 
@@ -105,6 +105,7 @@ def load_library(path=None):
     L.icp_get_block_trace.argtypes = [vp, _dp]
     L.icp_batch_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
                                 C.POINTER(C.c_int64), C.c_int, C.c_double, C.c_int, _ip, _dp, C.c_void_p, _dp]
+    L.icp_find_alignment_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     L.icp_batch_kernels_launched.restype = C.c_longlong
     L.icp_batch_run_multi.argtypes = [C.POINTER(C.c_int), C.c_int] + list(L.icp_batch_run.argtypes[1:])
     L.icp_group_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
