@@ -562,6 +562,8 @@ def main():
         os.environ["ICP_NN"] = "tree"        # read by icp_create (every context, batch lanes included)
     elif os.environ.get("ICP_NN") == "tree":
         args.nn = "tree"
+    else:
+        os.environ["ICP_NN"] = "brute"       # the metric counts executed brute-force pairs: no automatic tree on small clouds
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -89,14 +89,16 @@ int icp_get_scene(icp_ctx* ctx, double* p_xyz_out);
 int icp_reset_scene(icp_ctx* ctx);
 
 /* ---- how icp_closest / icp_run search (results are identical) ---------------
- * ICP_NN_BRUTE (default)  exact brute force: every scene point meets every model point (north_star).
+ * ICP_NN_AUTO (default)   brute force - except inside icp_run (>= 2 iterations) on clouds too small for the brute-force
+ *                         kernel to fill one wave of the GPU (up to ~16 384 x 16 384 points; cow), which take the tree.
+ * ICP_NN_BRUTE            exact brute force: every scene point meets every model point (north_star).
  * ICP_NN_TREE             exact search through a bounding-box hierarchy over the Morton-sorted model,
  *                         built on the device at the first search after icp_set_model; same first-minimum
  *                         rule on the reference's FP64 expression (src/cpu.cc:16-22), bit-identical
  *                         indices.  Also selected by ICP_NN=tree in the environment at icp_create.
  *                         Models whose extent is outside [1e-12, 1e12] keep the brute-force path
  *                         (icp_get_nn_mode reports what is in effect). */
-enum { ICP_NN_BRUTE = 0, ICP_NN_TREE = 1 };
+enum { ICP_NN_BRUTE = 0, ICP_NN_TREE = 1, ICP_NN_AUTO = 2 };
 int icp_set_nn_mode(icp_ctx* ctx, int mode);
 int icp_get_nn_mode(icp_ctx* ctx);
 

@@ -105,8 +105,10 @@ struct icp_ctx {
     uint32_t *d_keys = nullptr, *d_keys_alt = nullptr; int32_t* d_vals = nullptr; void* d_cub = nullptr;
     size_t cub_bytes = 0, sort_cap = 0;
     int32_t* d_vals_alt = nullptr;         // sorted values of the model's Morton sort (tree build)
-    // exact tree search, opt-in: ICP_NN=tree / icp_set_nn_mode
-    int nn_mode = ICP_NN_BRUTE;
+    // how K1 searches: ICP_NN=brute|tree|auto / icp_set_nn_mode.  auto (default): brute force, except inside icp_run on clouds
+    // too small for the brute-force filter to fill one wave of the GPU, which take the exact tree search (same indices)
+    int nn_mode = ICP_NN_AUTO;
+    bool auto_tree_now = false;            // auto mode: icp_run decided for the tree on the current clouds
     TreeDev tree;
     bool tree_built[2] = {false, false};   // [0] binary form, [1] wide form: built on first use, for the model currently set
     int tree_form = 0;                     // ICP_TREE: 0 auto, 1 wide (warp per point, 32-ary), 2 binary (thread per point)
@@ -166,10 +168,29 @@ int ensure_sort(icp_ctx* c, size_t n)
     return ICP_OK;
 }
 
+int env_nn_mode()
+{
+    const char* e = getenv("ICP_NN");
+    if (e && !strcmp(e, "tree")) return ICP_NN_TREE;
+    if (e && !strcmp(e, "brute")) return ICP_NN_BRUTE;
+    return ICP_NN_AUTO;
+}
+
+// auto mode's rule for icp_run: the brute-force filter's grid would be less than one full wave (2 CTAs per SM), i.e. the
+// clouds are too small for that kernel to approach its roofline whatever is done (cow: 48 CTAs of 296; up to ~16 384 x
+// 16 384 points), and an iteration is three kernel latencies.  There the tree search wins by 25 % resident and end to end
+// including the build (cow 7 iterations 0.34 -> 0.25 ms, profiles/r02f_tree_wl_cow.json); above, brute force stays.
+bool small_for_brute(const icp_ctx* c)
+{
+    const long long total = (c->s.np_pad / NN_TILE) * (c->m.nm_pad / NN_G);
+    return total / (NN_TM / NN_G) < (long long)c->sm_count * NN_MIN_CTAS;
+}
+
 // Rm = 0: every model point coincides with c0; the surrogate is then the same for all of them and FP64 decides.
 bool tree_active(const icp_ctx* c)
 {
-    return c->nn_mode == ICP_NN_TREE && (c->h_Rm == 0.0 || (c->h_Rm >= 1e-12 && c->h_Rm <= 1e12));
+    const bool wanted = c->nn_mode == ICP_NN_TREE || (c->nn_mode == ICP_NN_AUTO && c->auto_tree_now);
+    return wanted && (c->h_Rm == 0.0 || (c->h_Rm >= 1e-12 && c->h_Rm <= 1e12));
 }
 
 // Which form searches the current scene: ICP_TREE forces one; otherwise a warp per point while the scene is small.
@@ -444,7 +465,7 @@ static int create_body(icp_ctx* c, int device)
     if (const char* e = getenv("ICP_PROFILE")) c->profile = atoi(e) != 0;
     if (const char* e = getenv("ICP_LOOKAHEAD")) c->lookahead = atoi(e);
     if (const char* e = getenv("ICP_TREE")) c->tree_form = !strcmp(e, "wide") ? 1 : (!strcmp(e, "binary") ? 2 : 0);
-    if (const char* e = getenv("ICP_NN")) c->nn_mode = !strcmp(e, "tree") ? ICP_NN_TREE : ICP_NN_BRUTE;
+    c->nn_mode = env_nn_mode();
     if (const char* e = getenv("ICP_EXACT")) c->exact_mode = !strcmp(e, "inline") ? 1 : (!strcmp(e, "kernel") ? 2 : 0);
     CK(cudaHostAlloc((void**)&c->h_progress, sizeof(int), cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer((void**)&c->d_progress, c->h_progress, 0));
@@ -595,8 +616,9 @@ int icp_reset_scene(icp_ctx* c)
 
 int icp_set_nn_mode(icp_ctx* c, int mode)
 {
-    if (!c || (mode != ICP_NN_BRUTE && mode != ICP_NN_TREE)) { g_err = "icp_set_nn_mode: bad arguments"; return ICP_ERR_INVALID; }
+    if (!c || (mode != ICP_NN_BRUTE && mode != ICP_NN_TREE && mode != ICP_NN_AUTO)) { g_err = "icp_set_nn_mode: bad arguments"; return ICP_ERR_INVALID; }
     c->nn_mode = mode;
+    c->auto_tree_now = false;
     return ICP_OK;
 }
 
@@ -639,6 +661,7 @@ int icp_closest(icp_ctx* c, int32_t* idx_out, double* Y_out)
     CK(cudaSetDevice(c->device));
     int r;
     if ((r = reset_ctl(c))) return r;
+    c->auto_tree_now = false;             // auto mode: a single search does not pay for building the hierarchy
     if ((r = ensure_tree(c))) return r;
     c->stats.kernels_launched = 0;
     CK(cudaEventRecord(c->ev0, c->st));
@@ -779,6 +802,7 @@ int icp_run(icp_ctx* c, int max_iter, double threshold, int check_sizes, int* it
         c->ev_filter.push_back(e);
     }
     if ((r = reset_ctl(c))) return r;
+    c->auto_tree_now = c->nn_mode == ICP_NN_AUTO && max_iter >= 2 && small_for_brute(c);
     if ((r = ensure_tree(c))) return r;
     c->stats.kernels_launched = 0;
     CK(cudaEventRecord(c->ev0, c->st));
@@ -909,8 +933,8 @@ static thread_local icp_ctx* t_oneshot = nullptr;
 // as it is when they are used, not as it was when they were created.
 static void apply_env_nn(icp_ctx* c)
 {
-    const char* e = getenv("ICP_NN");
-    c->nn_mode = (e && !strcmp(e, "tree")) ? ICP_NN_TREE : ICP_NN_BRUTE;
+    c->nn_mode = env_nn_mode();
+    const char* e;
     e = getenv("ICP_EXACT");
     c->exact_mode = (e && !strcmp(e, "inline")) ? 1 : ((e && !strcmp(e, "kernel")) ? 2 : 0);
 }

@@ -200,8 +200,9 @@ class Context:
         _ck(self._L.icp_reset_scene(self._h))
 
     def set_nn_mode(self, mode):
-        """'brute' (default, north_star) or 'tree' (exact bounding-box hierarchy); same results."""
-        _ck(self._L.icp_set_nn_mode(self._h, {"brute": 0, "tree": 1}[mode]))
+        """'auto' (default: brute force, the tree inside run() on small clouds), 'brute' (north_star) or 'tree' (exact
+        bounding-box hierarchy); same results.  nn_mode() reports what the last search used."""
+        _ck(self._L.icp_set_nn_mode(self._h, {"brute": 0, "tree": 1, "auto": 2}[mode]))
 
     def nn_mode(self):
         return ("brute", "tree")[self._L.icp_get_nn_mode(self._h)]
@@ -325,7 +326,7 @@ class Group:
         _ck(self._L.icp_group_reset_scene(self._h))
 
     def set_nn_mode(self, mode):
-        _ck(self._L.icp_group_set_nn_mode(self._h, {"brute": 0, "tree": 1}[mode]))
+        _ck(self._L.icp_group_set_nn_mode(self._h, {"brute": 0, "tree": 1, "auto": 2}[mode]))
 
     def closest(self, want_idx=True, want_Y=True):
         idx = np.empty(self.np, np.int32) if want_idx else None

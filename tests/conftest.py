@@ -13,6 +13,12 @@ for p in (ROOT, PKG_DIR):
         sys.path.insert(0, p)
 
 
+# The library's default search mode is "auto" (brute force, the tree inside icp_run on small clouds).  The suite pins "brute" so
+# that every test of the brute-force kernels keeps testing them on small inputs too; tree tests select the tree explicitly, and
+# the auto rule has its own tests (which remove the variable).
+os.environ.setdefault("ICP_NN", "brute")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

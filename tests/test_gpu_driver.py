@@ -65,11 +65,15 @@ def test_tree_search_driver_writes_the_same_bytes(tmp_path, cloud_dir):
     ref, scene = cloud_text_path("cow_ref", cloud_dir), cloud_text_path("cow_tr1", cloud_dir)
     (tmp_path / "a").mkdir()
     (tmp_path / "b").mkdir()
-    ra = run_icp([ref, scene, "10"], tmp_path / "a")
+    ra = run_icp([ref, scene, "10"], tmp_path / "a", env={"ICP_NN": "brute"})
     rb = run_icp([ref, scene, "10"], tmp_path / "b", env={"ICP_NN": "tree"})
     assert ra.returncode == rb.returncode == 0
     assert ra.stderr == rb.stderr and ra.stdout == rb.stdout
     assert (tmp_path / "a" / "output.txt").read_bytes() == (tmp_path / "b" / "output.txt").read_bytes()
+    (tmp_path / "c").mkdir()                           # the library's default ("auto": the tree on a cloud of cow's size)
+    rc = run_icp([ref, scene, "10"], tmp_path / "c", env={"ICP_NN": "auto"})
+    assert rc.returncode == 0 and rc.stderr == ra.stderr
+    assert (tmp_path / "a" / "output.txt").read_bytes() == (tmp_path / "c" / "output.txt").read_bytes()
 
 
 def test_two_gpu_driver_writes_the_same_bytes(tmp_path, cloud_dir):

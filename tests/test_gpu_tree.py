@@ -218,3 +218,35 @@ def test_tree_full_size_property_4m(icp):
     idx, _ = ctx.closest(want_Y=False)
     assert np.array_equal(idx, perm.astype(np.int32))
     ctx.close()
+
+
+def test_auto_mode_takes_the_tree_only_inside_loops_on_small_clouds(icp, clouds, golden, monkeypatch):
+    # default mode (ICP_NN unset): icp_run on clouds too small to fill one wave of the brute-force filter searches through
+    # the tree - same indices, iteration count and error history as the golden vectors; a one-shot icp_closest and any
+    # cloud above the limit stay brute force
+    monkeypatch.delenv("ICP_NN", raising=False)
+    g = golden("cow_tr1")
+    ctx = icp.Context(0)
+    ctx.set_model(clouds("cow_ref"))
+    ctx.set_scene(clouds("cow_tr1"))
+    idx, _ = ctx.closest(want_Y=False)
+    assert ctx.nn_mode() == "brute" and np.array_equal(idx, g["idx_first"])
+    ctx.reset_scene()
+    it, hist = ctx.run(30)
+    assert ctx.nn_mode() == "tree"
+    assert it == int(g["iters"]) and np.all(np.abs(hist - g["err"]) <= 1e-5 * np.abs(g["err"]))
+    assert np.array_equal(ctx.indices(), g["idx_last"]) and np.abs(ctx.get_scene() - g["new_p"]).max() < 1e-9
+    ctx.reset_scene()
+    it1, _ = ctx.run(1)                                   # a single iteration does not pay for the build
+    assert it1 == 1 and ctx.nn_mode() == "brute"
+    ctx.set_nn_mode("brute")
+    ctx.reset_scene()
+    it_b, hist_b = ctx.run(30)
+    assert ctx.nn_mode() == "brute" and it_b == it and np.array_equal(hist_b, hist)      # everything after idx is shared code
+    ctx.set_nn_mode("auto")
+    g2 = golden("horse_tr2")
+    ctx.set_model(clouds("horse_ref"))
+    ctx.set_scene(clouds("horse_tr2"))
+    it2, _ = ctx.run(30)
+    assert ctx.nn_mode() == "brute" and it2 == int(g2["iters"]) and np.array_equal(ctx.indices(), g2["idx_last"])
+    ctx.close()
