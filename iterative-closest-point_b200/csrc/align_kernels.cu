@@ -129,38 +129,33 @@ __device__ __forceinline__ void moments_accumulate(double (&acc)[17], double ax,
     acc[16] += bx * bx + by * by + bz * bz;
 }
 
-__device__ __forceinline__ void moments_points(const Pt64* __restrict__ m64, const double* __restrict__ p64x,
+// Y = the matched model points, written by the search kernels (SceneDev::y64*): p and Y are streamed, nothing is gathered.
+struct MatchIn {
+    const double *yx, *yy, *yz;
+};
+
+__device__ __forceinline__ void moments_points(const MatchIn y, const double* __restrict__ p64x,
                                                const double* __restrict__ p64y, const double* __restrict__ p64z,
-                                               const int32_t* __restrict__ idx, int np, int nm, int n_blocks, double c0x,
-                                               double c0y, double c0z, double (&acc)[17], int* ctl)
+                                               int np, int n_blocks, double c0x, double c0y, double c0z, double (&acc)[17])
 {
     const int stride = n_blocks * RED_THREADS;
     int j = blockIdx.x * RED_THREADS + threadIdx.x;
-    for (; j + stride < np; j += 2 * stride) {
-        int k0 = idx[j], k1 = idx[j + stride];
-        ICP_CHK_IDX(k0, nm, ctl);
-        ICP_CHK_IDX(k1, nm, ctl);
+    for (; j + stride < np; j += 2 * stride) {          // two points in flight per thread
         const double a0x = p64x[j], a0y = p64y[j], a0z = p64z[j];
         const double a1x = p64x[j + stride], a1y = p64y[j + stride], a1z = p64z[j + stride];
-        double b0x, b0y, b0z, b1x, b1y, b1z;
-        ld_pt64(m64, k0, b0x, b0y, b0z);
-        ld_pt64(m64, k1, b1x, b1y, b1z);
+        const double b0x = y.yx[j], b0y = y.yy[j], b0z = y.yz[j];
+        const double b1x = y.yx[j + stride], b1y = y.yy[j + stride], b1z = y.yz[j + stride];
         moments_accumulate(acc, a0x - c0x, a0y - c0y, a0z - c0z, b0x - c0x, b0y - c0y, b0z - c0z);
         moments_accumulate(acc, a1x - c0x, a1y - c0y, a1z - c0z, b1x - c0x, b1y - c0y, b1z - c0z);
     }
-    if (j < np) {
-        int k = idx[j];
-        ICP_CHK_IDX(k, nm, ctl);
-        double bx, by, bz;
-        ld_pt64(m64, k, bx, by, bz);
-        moments_accumulate(acc, p64x[j] - c0x, p64y[j] - c0y, p64z[j] - c0z, bx - c0x, by - c0y, bz - c0z);
-    }
+    if (j < np)
+        moments_accumulate(acc, p64x[j] - c0x, p64y[j] - c0y, p64z[j] - c0z, y.yx[j] - c0x, y.yy[j] - c0y, y.yz[j] - c0z);
 }
 
 __global__ void __launch_bounds__(RED_THREADS, 4)
-moments_kernel(const Pt64* __restrict__ m64, int nm,
+moments_kernel(const MatchIn y,
                const double* __restrict__ geo, const double* __restrict__ p64x, const double* __restrict__ p64y,
-               const double* __restrict__ p64z, const int32_t* __restrict__ idx, int np, double* __restrict__ partials,
+               const double* __restrict__ p64z, int np, double* __restrict__ partials,
                double* __restrict__ mom, int* __restrict__ ctl, int honor_done, double* __restrict__ xf_fused,
                PeerComm pc)
 {
@@ -173,7 +168,7 @@ moments_kernel(const Pt64* __restrict__ m64, int nm,
     double acc[17];
 #pragma unroll
     for (int i = 0; i < 17; ++i) acc[i] = 0.0;
-    moments_points(m64, p64x, p64y, p64z, idx, np, nm, (int)gridDim.x, c0x, c0y, c0z, acc, ctl);
+    moments_points(y, p64x, p64y, p64z, np, (int)gridDim.x, c0x, c0y, c0z, acc);
     block_sum<17>(acc, red);
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -402,17 +397,14 @@ struct XfPoint {
     bool act;
 };
 
-__device__ __forceinline__ XfPoint xf_load(const Pt64* __restrict__ m64, int nm, const double* __restrict__ p64x,
-                                           const double* __restrict__ p64y, const double* __restrict__ p64z,
-                                           const int32_t* __restrict__ idx, int np, int j0, int* ctl)
+__device__ __forceinline__ XfPoint xf_load(const MatchIn y, const double* __restrict__ p64x,
+                                           const double* __restrict__ p64y, const double* __restrict__ p64z, int np, int j0)
 {
     XfPoint q;
     q.act = j0 < np;
     q.j = q.act ? j0 : np - 1;         // inactive lanes of the last warp re-read point np-1, which lives in this same warp
-    int k = idx[q.j];
-    ICP_CHK_IDX(k, nm, ctl);
     q.x = p64x[q.j]; q.y = p64y[q.j]; q.z = p64z[q.j];
-    ld_pt64(m64, k, q.mx, q.my, q.mz);
+    q.mx = y.yx[q.j]; q.my = y.yy[q.j]; q.mz = y.yz[q.j];
     return q;
 }
 
@@ -444,22 +436,22 @@ __device__ __forceinline__ void xf_apply(const XfPoint& q, int j0, double* __res
     }
 }
 
-__device__ __forceinline__ void transform_points(const Pt64* __restrict__ m64, int nm, double* __restrict__ p64x,
+__device__ __forceinline__ void transform_points(const MatchIn y, double* __restrict__ p64x,
                                                  double* __restrict__ p64y, double* __restrict__ p64z,
                                                  float* __restrict__ phx, float* __restrict__ phy,
-                                                 float* __restrict__ phz, const int32_t* __restrict__ idx, int np,
+                                                 float* __restrict__ phz, int np,
                                                  int np_pad, const double (&sr)[9], double tx, double ty, double tz,
                                                  double c0x, double c0y, double c0z, int in_place, int n_blocks,
-                                                 double& acc, int* ctl)
+                                                 double& acc)
 {
     const int np_round = (np + 31) & ~31;
     const int stride = n_blocks * RED_THREADS;
     for (int jA = blockIdx.x * RED_THREADS + threadIdx.x; jA < np_round; jA += 2 * stride) {
         const int jB = jA + stride;
         const bool hasB = jB < np_round;              // warp-uniform (32 consecutive, 32-aligned indices per warp)
-        const XfPoint A = xf_load(m64, nm, p64x, p64y, p64z, idx, np, jA, ctl);
+        const XfPoint A = xf_load(y, p64x, p64y, p64z, np, jA);
         XfPoint B = A;
-        if (hasB) B = xf_load(m64, nm, p64x, p64y, p64z, idx, np, jB, ctl);
+        if (hasB) B = xf_load(y, p64x, p64y, p64z, np, jB);
         // every lane has READ its points before any lane of this warp writes (only the warp that holds point np-1 has
         // inactive lanes, and they re-read that very point)
         __syncwarp();
@@ -476,10 +468,10 @@ __device__ __forceinline__ void transform_points(const Pt64* __restrict__ m64, i
 // finish = 1: the last block also closes the ICP iteration (src/cpu.cc:67-77): the reference adds the
 // two residual sums, which are the same expression evaluated twice, so err = 2*sum/np.
 __global__ void __launch_bounds__(RED_THREADS)
-transform_kernel(const Pt64* __restrict__ m64, int nm,
+transform_kernel(const MatchIn y,
                  const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
                  double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
-                 const int32_t* __restrict__ idx, int np, int np_pad, const double* __restrict__ xf, int in_place,
+                 int np, int np_pad, const double* __restrict__ xf, int in_place,
                  double* __restrict__ partials, double* __restrict__ err_sum, int* __restrict__ ctl, int honor_done,
                  int finish, double n_global, double threshold, double* __restrict__ err_hist, PeerComm pc)
 {
@@ -495,8 +487,8 @@ transform_kernel(const Pt64* __restrict__ m64, int nm,
     const double tx = xf[10], ty = xf[11], tz = xf[12];
     const double c0x = geo[0], c0y = geo[1], c0z = geo[2];
     double acc[1] = {0.0};
-    transform_points(m64, nm, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
-                     in_place, (int)gridDim.x, acc[0], ctl);
+    transform_points(y, p64x, p64y, p64z, phx, phy, phz, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
+                     in_place, (int)gridDim.x, acc[0]);
     block_sum<1>(acc, red);
     if (threadIdx.x == 0) {
         partials[blockIdx.x] = acc[0];
@@ -560,10 +552,10 @@ __global__ void finish_kernel(const double* __restrict__ err_sum, double n_globa
 #define ICP_FUSED_MIN_CTAS 3
 #endif
 __global__ void __launch_bounds__(RED_THREADS, ICP_FUSED_MIN_CTAS)
-align_fused_kernel(const Pt64* __restrict__ m64, int nm,
+align_fused_kernel(const MatchIn y,
                    const double* __restrict__ geo, double* __restrict__ p64x, double* __restrict__ p64y,
                    double* __restrict__ p64z, float* __restrict__ phx, float* __restrict__ phy, float* __restrict__ phz,
-                   const int32_t* __restrict__ idx, int np, int np_pad, double* __restrict__ partials,
+                   int np, int np_pad, double* __restrict__ partials,
                    double* __restrict__ mom, double* __restrict__ xf, double* __restrict__ err_sum,
                    int* __restrict__ ctl, int honor_done, int in_place, int finish, double n_global, double threshold,
                    double* __restrict__ err_hist, PeerComm pc, unsigned long long* __restrict__ trace)
@@ -594,7 +586,7 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     double acc[17];
 #pragma unroll
     for (int i = 0; i < 17; ++i) acc[i] = 0.0;
-    moments_points(m64, p64x, p64y, p64z, idx, np, nm, nb, c0x, c0y, c0z, acc, ctl);
+    moments_points(y, p64x, p64y, p64z, np, nb, c0x, c0y, c0z, acc);
     TRACE(1);
     block_sum<17>(acc, red);
     if (threadIdx.x == 0)
@@ -656,8 +648,8 @@ align_fused_kernel(const Pt64* __restrict__ m64, int nm,
     for (int i = 0; i < 9; ++i) sr[i] = __dmul_rn(s, xf_s[1 + i]);
     const double tx = xf_s[10], ty = xf_s[11], tz = xf_s[12];
     double e[1] = {0.0};
-    transform_points(m64, nm, p64x, p64y, p64z, phx, phy, phz, idx, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
-                     in_place, nb, e[0], ctl);
+    transform_points(y, p64x, p64y, p64z, phx, phy, phz, np, np_pad, sr, tx, ty, tz, c0x, c0y, c0z,
+                     in_place, nb, e[0]);
     TRACE(6);
     block_sum<1>(e, red);
     if (threadIdx.x == 0) {
@@ -887,6 +879,19 @@ __global__ void indices_export_kernel(int64_t np, const int32_t* __restrict__ pe
     }
 }
 
+// Y = m64[idx] for every scene point: only where idx was set from outside the search kernels
+__global__ void gather_matches_kernel(int64_t np, int nm, const int32_t* __restrict__ idx, const Pt64* __restrict__ m64,
+                                      double* __restrict__ yx, double* __restrict__ yy, double* __restrict__ yz)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np) return;
+    int k = idx[i];
+    if ((unsigned)k >= (unsigned)nm) k = 0;
+    double x, y, z;
+    ld_pt64(m64, k, x, y, z);
+    yx[i] = x; yy[i] = y; yz[i] = z;
+}
+
 // mu_p, mu_y from the moments (src/cpu.cc:113-114)
 __global__ void centroid_export_kernel(const double* __restrict__ geo, const double* __restrict__ mom,
                                        double* __restrict__ out6)
@@ -986,7 +991,7 @@ void launch_moments(const ModelDev& m, const SceneDev& s, double* partials, int 
 {
     PeerComm pc;
     if (peer) pc = *peer;
-    moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64, (int)m.nm, m.geo, s.p64x, s.p64y, s.p64z, s.idx,
+    moments_kernel<<<n_blocks, RED_THREADS, 0, st>>>(MatchIn{s.y64x, s.y64y, s.y64z}, m.geo, s.p64x, s.p64y, s.p64z,
                                                      (int)s.np, partials, mom, ctl, honor_done, xf_fused, pc);
 }
 
@@ -1001,8 +1006,8 @@ void launch_transform(const ModelDev& m, const SceneDev& s, const double* xf, in
 {
     PeerComm pc;
     if (peer) pc = *peer;
-    transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(m.m64, (int)m.nm, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
-                                                       s.phy, s.phz, s.idx, (int)s.np, (int)s.np_pad, xf, in_place,
+    transform_kernel<<<n_blocks, RED_THREADS, 0, st>>>(MatchIn{s.y64x, s.y64y, s.y64z}, m.geo, s.p64x, s.p64y, s.p64z, s.phx,
+                                                       s.phy, s.phz, (int)s.np, (int)s.np_pad, xf, in_place,
                                                        partials, err_sum, ctl, honor_done, finish, n_global,
                                                        threshold, err_hist, pc);
 }
@@ -1024,13 +1029,11 @@ int launch_align_fused(const ModelDev& m, const SceneDev& s, double* partials, i
     PeerComm pc;
     if (peer) pc = *peer;
     int np = (int)s.np, np_pad = (int)s.np_pad;
-    const Pt64* a0 = m.m64;
-    int nm = (int)m.nm;
+    MatchIn a0{s.y64x, s.y64y, s.y64z};
     const double* a3 = m.geo;
     double *b0 = s.p64x, *b1 = s.p64y, *b2 = s.p64z;
     float *f0 = s.phx, *f1 = s.phy, *f2 = s.phz;
-    const int32_t* ix = s.idx;
-    void* args[] = {&a0, &nm, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &ix, &np, &np_pad, &partials, &mom, &xf, &err_sum,
+    void* args[] = {&a0, &a3, &b0, &b1, &b2, &f0, &f1, &f2, &np, &np_pad, &partials, &mom, &xf, &err_sum,
                     &ctl, &honor_done, &in_place, &finish, &n_global, &threshold, &err_hist, &pc, &trace};
     return (int)cudaLaunchCooperativeKernel((const void*)align_fused_kernel, dim3(n_blocks), dim3(RED_THREADS), args, 0, st);
 }
@@ -1083,6 +1086,11 @@ void launch_scene_export(const SceneDev& s, double* xyz_aos_out, cudaStream_t st
 void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_out, double* Y_aos_out, cudaStream_t st)
 {
     indices_export_kernel<<<grid1d(s.np, 256), 256, 0, st>>>(s.np, s.perm, s.idx, m.m64, (int)m.nm, idx_out, Y_aos_out);
+}
+
+void launch_gather_matches(const SceneDev& s, const ModelDev& m, cudaStream_t st)
+{
+    gather_matches_kernel<<<grid1d(s.np, 256), 256, 0, st>>>(s.np, (int)m.nm, s.idx, m.m64, s.y64x, s.y64y, s.y64z);
 }
 
 void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st)

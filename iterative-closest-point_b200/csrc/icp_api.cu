@@ -332,7 +332,10 @@ void nn_pass(icp_ctx* c, int honor_done, int use_prev, cudaEvent_t e0, cudaEvent
     }
     // Model point 0 is NaN: d(0) is NaN for every scene point and minCoeff's strict `<` never replaces it
     // (src/cpu.cc:21-22), so the reference matches everything to index 0; the kernels above ignore NaN candidates.
-    if (c->model0_nan) cudaMemsetAsync(c->s.idx, 0, (size_t)c->s.np * sizeof(int32_t), c->st);
+    if (c->model0_nan) {
+        cudaMemsetAsync(c->s.idx, 0, (size_t)c->s.np * sizeof(int32_t), c->st);
+        launch_gather_matches(c->s, c->m, c->st);
+    }
     if (e1) cudaEventRecord(e1, c->st);
     if (e2) cudaEventRecord(e2, c->st);
     if (e3) cudaEventRecord(e3, c->st);
@@ -509,6 +512,7 @@ void icp_destroy(icp_ctx* c)
     dfree(c->m.m64); dfree(c->m.mhat); dfree(c->m.geo);
     dfree(c->s.p64x); dfree(c->s.p64y); dfree(c->s.p64z); dfree(c->s.q64x); dfree(c->s.q64y); dfree(c->s.q64z);
     dfree(c->s.phx); dfree(c->s.phy); dfree(c->s.phz); dfree(c->s.perm); dfree(c->s.idx);
+    dfree(c->s.y64x); dfree(c->s.y64y); dfree(c->s.y64z);
     dfree(c->sc.best); dfree(c->sc.runner); dfree(c->sc.chunk); dfree(c->sc.amb_list); dfree(c->sc.amb_thr);
     dfree(c->d_stage); dfree(c->d_partials); dfree(c->d_mom); dfree(c->d_xf); dfree(c->d_err_sum); dfree(c->d_out6);
     dfree(c->d_err_hist); dfree(c->d_ctl); dfree(c->d_keys); dfree(c->d_keys_alt); dfree(c->d_vals);
@@ -578,7 +582,9 @@ int icp_set_scene(icp_ctx* c, const double* p_xyz, int64_t np)
             (r = dalloc(&c->s.q64y, (size_t)np_pad)) || (r = dalloc(&c->s.q64z, (size_t)np_pad)) ||
             (r = dalloc(&c->s.phx, (size_t)np_pad)) || (r = dalloc(&c->s.phy, (size_t)np_pad)) ||
             (r = dalloc(&c->s.phz, (size_t)np_pad)) || (r = dalloc(&c->s.perm, (size_t)np_pad)) ||
-            (r = dalloc(&c->s.idx, (size_t)np_pad)) || (r = dalloc(&c->sc.amb_list, (size_t)np_pad)) ||
+            (r = dalloc(&c->s.idx, (size_t)np_pad)) || (r = dalloc(&c->s.y64x, (size_t)np_pad)) ||
+            (r = dalloc(&c->s.y64y, (size_t)np_pad)) || (r = dalloc(&c->s.y64z, (size_t)np_pad)) ||
+            (r = dalloc(&c->sc.amb_list, (size_t)np_pad)) ||
             (r = dalloc(&c->sc.amb_thr, (size_t)np_pad)))
             return r;
         c->cap_np = (size_t)np_pad;
@@ -986,6 +992,7 @@ static int pair_ctx(icp_ctx** out, const double* Y_xyz, const double* p_xyz, int
         g_err = "pair_ctx: copy failed";
         return ICP_ERR_CUDA;
     }
+    launch_gather_matches(c->s, c->m, c->st);
     c->have_idx = true;
     *out = c;
     return ICP_OK;

@@ -94,7 +94,18 @@ struct SceneDev {
     float *phx = nullptr, *phy = nullptr, *phz = nullptr;
     int32_t* perm = nullptr;     // sorted position -> original position
     int32_t* idx = nullptr;      // correspondence (sorted order)
+    // Y = the matched model point of every scene point (FP64 SoA, sorted order), written by whichever kernel decides the
+    // match (it has just read that model record for its FP64 evaluation).  K2 and K4 then STREAM p and Y instead of
+    // gathering m64[idx[j]]: a random 32-byte gather costs a 64-byte DRAM burst and a dependent idx -> m64 chain per point
+    // (ncu, 2^22 points: K2 read 78 B per point for 60 expected, profiles/r02b_syn4m_k2k4_split_metrics.csv).
+    double *y64x = nullptr, *y64y = nullptr, *y64z = nullptr;
 };
+
+struct MatchOut {                // where a search kernel records its decision for scene point j
+    int32_t* idx;
+    double *yx, *yy, *yz;
+};
+inline MatchOut match_out(const SceneDev& s) { return MatchOut{s.idx, s.y64x, s.y64y, s.y64z}; }
 
 struct NNScratch {
     int n_cta = 0;               // CTAs of the filter's single wave (stream-K decomposition)
@@ -184,6 +195,8 @@ void launch_scene_export(const SceneDev& s, double* xyz_aos_out, cudaStream_t st
 void launch_indices_export(const SceneDev& s, const ModelDev& m, int32_t* idx_out, double* Y_aos_out,
                            cudaStream_t st);
 void launch_centroid_export(const ModelDev& m, const double* mom, double* out6, cudaStream_t st);
+// idx[] was set from outside the search kernels (pairing by permutation, all-zero matches): rebuild Y = m64[idx]
+void launch_gather_matches(const SceneDev& s, const ModelDev& m, cudaStream_t st);
 void launch_subtract_col(const double* M_aos, int64_t n, double mx, double my, double mz, double* out_aos,
                          cudaStream_t st);
 
@@ -196,6 +209,17 @@ __device__ __forceinline__ void ld_pt64(const Pt64* __restrict__ a, int k, doubl
 {
     double w __attribute__((unused));
     asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(x), "=d"(y), "=d"(z), "=d"(w) : "l"(a + k));
+}
+// records the match of scene point j: the index and the model point itself (one 32-byte read, normally an L1 / L2 hit: the
+// deciding kernel evaluated that record in FP64 a moment ago)
+__device__ __forceinline__ void store_match(const MatchOut& mo, const Pt64* __restrict__ m64, int j, int k)
+{
+    double x, y, z;
+    ld_pt64(m64, k, x, y, z);
+    mo.idx[j] = k;
+    mo.yx[j] = x;
+    mo.yy[j] = y;
+    mo.yz[j] = z;
 }
 // A scene point with a NaN or infinite coordinate has only NaN / +inf distances; Eigen's minCoeff visitor starts at
 // column 0 and only moves on a strict `<` (src/cpu.cc:21-22), so the reference matches it to index 0.  Every search

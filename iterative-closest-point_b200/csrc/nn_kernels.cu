@@ -438,7 +438,7 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
                  const float* __restrict__ phx, const float* __restrict__ phy, const float* __restrict__ phz, int np,
                  int np_pad, int n_tiles, int cpt, int n_cta, const float* __restrict__ part_best,
                  const float* __restrict__ part_runner,
-                 const uint32_t* __restrict__ part_chunk, int32_t* __restrict__ idx, int32_t* __restrict__ amb_list,
+                 const uint32_t* __restrict__ part_chunk, MatchOut mo, int32_t* __restrict__ amb_list,
                  float* __restrict__ amb_thr, int* __restrict__ ctl, int honor_done, int inline_exact)
 {
     if (honor_done && ctl[CTL_DONE]) return;
@@ -515,7 +515,7 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
         const bool clear = runner > thr && thr < INF;                 // false for NaN/inf oddities too
 
         if (!scene_point_finite(px, py, pz)) {        // uniform per group: the reference's answer is index 0
-            if (sub == 0 && valid) idx[j] = 0;
+            if (sub == 0 && valid) store_match(mo, m64, j, 0);
         } else if (clear) {
             // ---- best chunk: FP32 surrogate against thr, FP64 only for the survivors ---------------
             const float ax = -2.0f * lx, ay = -2.0f * ly, az = -2.0f * lz;
@@ -540,7 +540,7 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
             double v = bt.v;
             int k = bt.k;
             group_argmin<RF>(v, k, gmask);             // `clear` is uniform per group, not per warp
-            if (sub == 0 && valid) idx[j] = first_min_or_zero(k);
+            if (sub == 0 && valid) store_match(mo, m64, j, first_min_or_zero(k));
         } else if (sub == 0 && valid) {
             if (inline_exact) {
                 const int pos = atomicAdd(&s_cnt, 1);
@@ -561,7 +561,7 @@ nn_refine_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, 
                 const int jq = s_j[a];
                 const int k = pruned_rescan(mhat, m64, nm, nm_pad, phx, phy, phz, p64x, p64y, p64z, part_best, np_pad, n_tiles,
                                             cpt, n_cta, jq, s_thr[a], sp, sv, sk);
-                if (threadIdx.x == 0) idx[jq] = first_min_or_zero(k);
+                if (threadIdx.x == 0) store_match(mo, m64, jq, first_min_or_zero(k));
             }
             if (threadIdx.x == 0) undecided += nq;
             __syncthreads();                         // s_j / s_cnt are rewritten by the next trip
@@ -582,7 +582,7 @@ nn_exact_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, i
                 const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
                 const float* __restrict__ phy, const float* __restrict__ phz, const float* __restrict__ part_best,
                 int np_pad, int n_tiles, int cpt, int n_cta, const int32_t* __restrict__ amb_list,
-                const float* __restrict__ amb_thr, int32_t* __restrict__ idx, int* __restrict__ ctl,
+                const float* __restrict__ amb_thr, MatchOut mo, int* __restrict__ ctl,
                 int honor_done, unsigned long long* __restrict__ trace)
 {
     if (honor_done && ctl[CTL_DONE]) return;
@@ -594,7 +594,7 @@ nn_exact_kernel(const Pt64* __restrict__ m64, const float4* __restrict__ mhat, i
         const int j = amb_list[a];
         const int k = pruned_rescan(mhat, m64, nm, nm_pad, phx, phy, phz, p64x, p64y, p64z, part_best, np_pad, n_tiles, cpt,
                                     n_cta, j, amb_thr[a], sp, sv, sk);
-        if (threadIdx.x == 0) idx[j] = first_min_or_zero(k);
+        if (threadIdx.x == 0) store_match(mo, m64, j, first_min_or_zero(k));
     }
     if (threadIdx.x == 0) {
         __threadfence();
@@ -631,7 +631,7 @@ void launch_nn_refine(const ModelDev& m, const SceneDev& s, const NNScratch& sc,
     nn_refine_kernel<<<(int)grid, REFINE_THREADS, 0, st>>>(m.m64, m.mhat, (int)m.nm, (int)m.nm_pad, m.geo, s.p64x, s.p64y,
                                                            s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)s.np_pad,
                                                            (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.n_cta,
-                                                           sc.best, sc.runner, sc.chunk, s.idx, sc.amb_list,
+                                                           sc.best, sc.runner, sc.chunk, match_out(s), sc.amb_list,
                                                            sc.amb_thr, ctl, honor_done, inline_exact);
 }
 
@@ -642,7 +642,7 @@ void launch_nn_exact(const ModelDev& m, const SceneDev& s, const NNScratch& sc, 
     nn_exact_kernel<<<grid, EXACT_THREADS, 0, st>>>(m.m64, m.mhat, (int)m.nm, (int)m.nm_pad, s.p64x,
                                                     s.p64y, s.p64z, s.phx, s.phy, s.phz, sc.best, (int)s.np_pad,
                                                     (int)(s.np_pad / NN_TILE), (int)(m.nm_pad / NN_G), sc.n_cta,
-                                                    sc.amb_list, sc.amb_thr, s.idx, ctl, honor_done, trace);
+                                                    sc.amb_list, sc.amb_thr, match_out(s), ctl, honor_done, trace);
 }
 
 }  // namespace icpb

@@ -173,7 +173,7 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
                const float4* __restrict__ mhat, const Pt64* __restrict__ m64, const double* __restrict__ geo, const double* __restrict__ p64x,
                const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
                const float* __restrict__ phy, const float* __restrict__ phz, int np, int nm,
-               int32_t* __restrict__ idx, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
+               MatchOut mo, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
 {
     publish_progress(progress, ctl);
     if (honor_done && ctl[CTL_DONE]) return;
@@ -184,7 +184,7 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
     q.px = phx[j]; q.py = phy[j]; q.pz = phz[j];
     q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
     q.m64 = m64;
-    if (!scene_point_finite(q.qx, q.qy, q.qz)) { idx[j] = 0; return; }
+    if (!scene_point_finite(q.qx, q.qy, q.qz)) { store_match(mo, m64, j, 0); return; }
     {
         const float Rm = __fmul_ru(__double2float_ru(geo[3]), 1.000001f);
         const float H = __fsqrt_ru(__fmaf_ru(q.pz, q.pz, __fmaf_ru(q.py, q.py, __fmul_ru(q.px, q.px))));
@@ -195,7 +195,7 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
     q.v = __longlong_as_double(0x7ff0000000000000LL);
     q.k = 0x7fffffff;
     if (use_prev) {      // last iteration's match: a near-optimal bound before the first node is opened
-        const int kp = idx[j];
+        const int kp = mo.idx[j];
         if (kp >= 0 && kp < nm) {
             const float4 m = mhat[kp];
             q.offer(surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z), kp);
@@ -248,7 +248,7 @@ nn_tree_kernel(const float* __restrict__ nodes, const float4* __restrict__ pts, 
             if (vv < bv) { bv = vv; q.k = kk; }
         }
     }
-    idx[j] = q.k;
+    store_match(mo, m64, j, q.k);
 }
 
 
@@ -467,7 +467,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
                 const float4* __restrict__ mhat, const Pt64* __restrict__ m64, const double* __restrict__ geo, const double* __restrict__ p64x,
                 const double* __restrict__ p64y, const double* __restrict__ p64z, const float* __restrict__ phx,
                 const float* __restrict__ phy, const float* __restrict__ phz, int np, int nm,
-                int32_t* __restrict__ idx, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
+                MatchOut mo, int use_prev, int* __restrict__ ctl, int honor_done, int* __restrict__ progress)
 {
     publish_progress(progress, ctl);
     if (honor_done && ctl[CTL_DONE]) return;
@@ -481,7 +481,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     q.qx = p64x[j]; q.qy = p64y[j]; q.qz = p64z[j];
     q.m64 = m64;
     if (!scene_point_finite(q.qx, q.qy, q.qz)) {            // warp-uniform
-        if (lane == 0) idx[j] = 0;
+        if (lane == 0) store_match(mo, m64, j, 0);
         return;
     }
     {
@@ -493,7 +493,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
     q.v = __longlong_as_double(0x7ff0000000000000LL);
     q.k = 0x7fffffff;
     if (use_prev) {
-        const int kp = idx[j];
+        const int kp = mo.idx[j];
         if (kp >= 0 && kp < nm) {
             const float4 m = mhat[kp];
             const float d2 = surrogate_direct(q.px, q.py, q.pz, m.x, m.y, m.z);
@@ -576,7 +576,7 @@ nn_wtree_kernel(const float* __restrict__ boxes, WideLevels lv, const float4* __
         }
         if (k == 0x7fffffff) k = 0;
     }
-    if (lane == 0) idx[j] = k;
+    if (lane == 0) store_match(mo, m64, j, k);
 }
 
 }  // namespace
@@ -691,7 +691,7 @@ void launch_nn_wtree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int
 {
     const int grid = (int)((s.np + WT_WARPS - 1) / WT_WARPS);
     nn_wtree_kernel<<<grid, WT_WARPS * 32, 0, st>>>(t.wboxes, t.w, t.wpts, m.mhat, m.m64, m.geo, s.p64x,
-                                                    s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm, s.idx,
+                                                    s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm, match_out(s),
                                                     use_prev, ctl, honor_done, progress);
 }
 
@@ -714,7 +714,7 @@ void launch_nn_tree(const ModelDev& m, const SceneDev& s, const TreeDev& t, int 
     const int grid = (int)((s.np + TREE_THREADS - 1) / TREE_THREADS);
     nn_tree_kernel<<<grid, TREE_THREADS, 0, st>>>(t.nodes, t.pts, t.n_leaves, m.mhat, m.m64, m.geo,
                                                   s.p64x, s.p64y, s.p64z, s.phx, s.phy, s.phz, (int)s.np, (int)m.nm,
-                                                  s.idx, use_prev, ctl, honor_done, progress);
+                                                  match_out(s), use_prev, ctl, honor_done, progress);
 }
 
 }  // namespace icpb
