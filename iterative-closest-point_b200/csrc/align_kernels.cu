@@ -4,8 +4,9 @@
 //   host Eigen::EigenSolver on Horn's N                             (src/cpu.cc:121-152, src/GPU/gpu.cc:106-140)
 //   compute_err (both uses)                                         (src/GPU/compute.cu:315-379; src/cpu.cc:29-40,93-103)
 //
-// K2 reads each scene point once (24 B) with its correspondence (4 B) and the gathered model point
-// (24 B) and accumulates 18 sums about the pivot c0 (centre of the model's bounding box):
+// K2 reads each scene point once (24 B) with its matched model point (24 B, streamed from SceneDev::y64*, where the
+// search kernel that decided the match recorded it; algorithmically: correspondence 4 B + gathered model point 24 B)
+// and accumulates 18 sums about the pivot c0 (centre of the model's bounding box):
 //   n, sum a, sum b, sum a b^T, sum |a|^2, sum |b|^2      with a = p - c0, b = y - c0.
 // Centring is algebraic (S = sum a b^T - n mu_a mu_b^T, ...), so the centred copies p', y' that the
 // reference materialises (src/cpu.cc:116-117) never exist.  Reduction is a fixed two-level tree
@@ -777,7 +778,7 @@ __global__ void model_geo_kernel(double* geo)
     geo[3] = sqrt(h2) * (1.0 + 1e-9);
 }
 
-// AoS FP64 model -> FP64 SoA master + FP32 float4 shadow (c0-relative), sentinel padding.
+// AoS FP64 model -> FP64 master (one 32-byte record per point) + FP32 float4 shadow (c0-relative), sentinel padding.
 __global__ void model_build_kernel(const double* __restrict__ xyz, int64_t nm, int64_t nm_pad,
                                    const double* __restrict__ geo, Pt64* __restrict__ m64, float4* __restrict__ mhat)
 {

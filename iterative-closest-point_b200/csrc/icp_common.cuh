@@ -1,12 +1,12 @@
 // icp_common.cuh — shared declarations of the B200-native ICP hot path (sm_100a only).
 //
 // Device data layout (everything resident in HBM for the life of a context):
-//   model   m64x/y/z  : FP64 SoA master, original order (indices returned are positions here)
+//   model   m64       : FP64 master, one 32-byte record (x,y,z,0) per point, original order (indices returned are positions here)
 //           mhat      : float4 (x,y,z,0) = fl32(m - c0), c0 = centre of the model's bounding box;
 //                       padded to a multiple of NN_TM with far-away sentinels
 //   scene   p64x/y/z  : FP64 SoA master of new_p, Morton-sorted (perm[i] = original position)
 //           phx/y/z   : FP32 shadow fl32(new_p - c0), padded to a multiple of NN_TILE
-//           idx       : int32 correspondence per sorted scene point
+//           idx, y64* : int32 correspondence per sorted scene point and the matched model point itself (FP64 SoA)
 //   scratch part_*    : per (model split, scene point) filter results; block partials of reductions
 //   state   xf[]      : s, R[9], t[3], mu_p[3], mu_y[3]; ctl[] : done flag, iteration counter, ...
 #pragma once

@@ -4,24 +4,26 @@
 // (src/GPU/compute.cu:94-150) — neither is ported.  The reference materialises an np x nm FP64
 // distance matrix in HBM and scans it with one thread per scene point; here nothing is
 // materialised: model tiles stream through shared memory and the running minimum stays in
-// registers.  Three kernels:
+// registers.  Three kernels (geometry constants in icp_common.cuh; the numbers below are the defaults):
 //
-//  nn_filter  FP32, CUDA cores, FMA-pipe bound.  Work item = (scene tile of 1024 points, model split).
+//  nn_filter  FP32, CUDA cores, issue bound.  Work = one linear sequence of (scene tile of 2048 points, 128-point model
+//             chunk) units cut into equal contiguous ranges, one per CTA ("stream-K", 2 CTAs per SM, whole waves).
 //             Model tiles (512 points) arrive by TMA bulk copy (cp.async.bulk + mbarrier) as float4,
 //             are re-expressed relative to the CTA's own origin and staged as SoA float4 planes
-//             X|Y|Z|W (W = |m|^2).  Each thread keeps 8 scene points in registers (coordinates
-//             pre-scaled by -2 and duplicated into f32x2 pairs) and evaluates, per LDS.128 of four
-//             consecutive model points,   d' = |m|^2 - 2 p.m   for 8 x 4 pairs with 48 FFMA2
-//             (fma.rn.f32x2) and 16 FMNMX3 (3-input min): 3 FMA-pipe lane-cycles and 2.1 issue
-//             slots per pair.  Only the VALUE of the minimum is tracked per pair; the index is
-//             recovered lazily: per 64-point model chunk the chunk minimum is merged into (best,
-//             best chunk id, runner-up over all other chunks).
-//  nn_refine  one warp per scene point: merges the model splits, derives a rigorous bound tau on
+//             X|Y|Z|W (W = |m|^2).  Each thread keeps 16 scene points in registers (coordinates
+//             pre-scaled by -2) and evaluates, per LDS.128 of four consecutive model points,
+//             d' = |m|^2 - 2 p.m   for 16 x 4 pairs with 96 FFMA2 (fma.rn.f32x2) and 32 FMNMX3 (3-input min).
+//             Only the VALUE of the minimum is tracked per pair; the index is recovered lazily: per model chunk the
+//             chunk minimum is merged into (best, best chunk id, runner-up over all other chunks), one result per
+//             (scene tile, CTA) slot.
+//  nn_refine  8 lanes per scene point: merges the tile's slots, derives a rigorous bound tau on
 //             the FP32 evaluation error, and if the runner-up chunk is provably farther than tau
-//             re-ranks the 64 points of the best chunk in FP64 with the reference's own expression
-//             sqrt((dx*dx+dy*dy)+dz*dz), lowest index on ties (warp-shuffle argmin).  Otherwise the
-//             point is queued for
-//  nn_exact   a full FP64 scan of the model for the (rare) ambiguous points.
+//             re-ranks the points of the best chunk in FP64 with the reference's own expression
+//             sqrt((dx*dx+dy*dy)+dz*dz), lowest index on ties (shuffle argmin).  Otherwise the point is undecided:
+//             the chunk ranges of the slots whose minimum is within the threshold are rescanned (pruned_rescan) -
+//             by the block itself while such a range is short, else the point is queued for
+//  nn_exact   one block per queued point, the same pruned rescan (large clouds only).
+//  Every decision is recorded as (index, the matched model point) - store_match - so that K2 / K4 gather nothing.
 //
 // Error bound (DESIGN.md §K1 has the derivation).  With u = 2^-24, P = |p_loc|, r = FP32 distance of
 // the filter's winner, M = P + r (largest |m_loc| a relevant candidate can have):
@@ -79,8 +81,8 @@ constexpr int SOA_BUF = 4 * SOA_PLANE;                 // floats per buffer (X|Y
 constexpr size_t FILTER_SMEM = NN_TM * sizeof(float4) + 2 * SOA_BUF * sizeof(float);
 
 // ------------------------------------------------------------------------------------------------
-// Work decomposition ("stream-K"): the np_pad/1024 scene tiles x cpt model chunks (64 points each) form one
-// linear sequence of T = n_tiles * cpt chunk-units, scene tile major.  The grid is ONE wave of CTAs (4 per SM)
+// Work decomposition ("stream-K"): the np_pad/NN_TILE scene tiles x cpt model chunks (NN_G points each) form one
+// linear sequence of T = n_tiles * cpt chunk-units, scene tile major.  The grid is whole waves of CTAs (NN_MIN_CTAS per SM)
 // and CTA b owns the contiguous range [b*T/n, (b+1)*T/n): every CTA gets the same work to within one chunk,
 // whatever the cloud sizes, so all SMs finish together.  A range may end inside a scene tile and continue in
 // the next one; each (CTA, scene tile) segment writes its own partial result into slot = b - first CTA of that
@@ -189,7 +191,7 @@ nn_filter_kernel(const float4* __restrict__ mhat, const float* __restrict__ phx,
                 bulk_g2s(raw, mhat + (size_t)(mt + 1) * NN_TM, NN_TM * sizeof(float4), &mbar);
             }
 
-            // ---- compute: 8 scene points x (up to) 512 model points per thread --------------------------
+            // ---- compute: NN_R scene points x (up to) 512 model points per thread -----------------------
             const float4* X4 = reinterpret_cast<const float4*>(buf);
             const float4* Y4 = reinterpret_cast<const float4*>(buf + SOA_PLANE);
             const float4* Z4 = reinterpret_cast<const float4*>(buf + 2 * SOA_PLANE);
